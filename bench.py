@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""Benchmark of the generation hot path (pga_run / pga_run_islands).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload onemax|rastrigin|test1|tsp] [--gens G]
+
+A "step" is one pga_run(G) call (G generations, default 100: the generation
+count of the reference's own test/test.cu:43) on the workload BASELINE.json's
+metric is quoted on: OneMax, 2^20 genomes x 1024 packed bits, one island per GPU.
+With N > 1 (torchrun, one rank per GPU) every rank holds one such island, the
+islands form a ring and the top 1 % migrate every 10 generations over NCCL
+(pga_run_islands): weak scaling.
+
+Prints ONE JSON line (rank 0).  value = genome-evaluations/s with the population
+resident in HBM; e2e = the same through the public API with the initial
+population uploaded from pinned host memory and the best individual read back
+every step.  --impl reference times the CPU oracle (the reference has no CPU
+implementation of its own; its GPU code is a 2013 sm_20 build that cannot run
+this workload) on all host cores.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (size, genome_len, encoding, builtin objective / hooks, genome bytes)
+    "onemax": dict(size=1 << 20, length=1024, bits=True, builtin="ONEMAX", label="C2 OneMax 2^20 x 1024 bits"),
+    "rastrigin": dict(size=1 << 20, length=256, bits=False, builtin="RASTRIGIN", label="C3 Rastrigin 2^20 x 256 f32"),
+    "test1": dict(size=40000, length=100, bits=False, hook="sum_obj", label="C1 test/test.cu 40000 x 100 f32, sum hook"),
+    "tsp": dict(size=1 << 22, length=100, bits=False, hook="tsp_obj", xover="tsp_crossover",
+                label="C4 test3 hooks 2^22 x 100 f32"),
+}
+
+
+def genome_bytes(w):
+    return w["length"] // 8 if w["bits"] else w["length"] * 4
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(workload):
+    """Per-launch DRAM bytes of the fused kernel from the committed ncu capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            return json.load(f).get(workload, {}).get("dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_solver(pg, w, seed, tsp=None):
+    g = pg.PGA(seed=seed)
+    return g
+
+
+def configure(pg, g, w):
+    if w.get("builtin"):
+        g.set_builtin_objective(getattr(pg, "OBJ_" + w["builtin"]))
+    if w.get("hook"):
+        g.set_objective_function(w["hook"])
+    if w.get("xover"):
+        g.set_crossover_function(w["xover"])
+    if w.get("hook") == "tsp_obj":
+        import numpy as np
+        with open(os.path.join(ROOT, "tests", "golden", "tsp100.txt")) as f:
+            tok = f.read().split()
+        n = int(tok[0])
+        g.tsp_load(np.array(tok[1:1 + n * n], dtype=np.float32).reshape(n, n))
+
+
+def run_reference_arm(args, w):
+    """The CPU oracle on all host cores: a bounded sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import pyoracle as po
+    cores = os.cpu_count() or 1
+    enc = po.GENES_BITS if w["bits"] else po.GENES_F32
+    o = po.Oracle(42, threads=cores)
+    pop = o.create_population(w["size"], w["length"], enc)
+    if w.get("builtin"):
+        o.set_builtin_objective(getattr(po, "OBJ_" + w["builtin"]))
+    if w.get("hook"):
+        o.set_objective_hook(w["hook"])
+    if w.get("xover"):
+        o.set_crossover_hook(w["xover"])
+    if w.get("hook") == "tsp_obj":
+        import numpy as np
+        with open(os.path.join(ROOT, "tests", "golden", "tsp100.txt")) as f:
+            tok = f.read().split()
+        n = int(tok[0])
+        o.tsp_load(np.array(tok[1:1 + n * n], dtype=np.float32).reshape(n, n))
+    o.evaluate(pop)
+    # size the per-step sample so the whole run stays within a few minutes
+    t0 = time.perf_counter(); o.run(1); per_gen = time.perf_counter() - t0
+    budget = 120.0 / max(1, args.steps + args.warmup)
+    gens = max(1, min(args.gens, int(budget / max(per_gen, 1e-6))))
+    for _ in range(args.warmup):
+        o.run(gens)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        o.run(gens)
+    dt = time.perf_counter() - t0
+    value = args.steps * gens * w["size"] / dt
+    sample = f"{gens} generations of {w['label']} per step at full population size, OpenMP over individuals"
+    o.close()
+    line = {
+        "impl": "reference", "metric": "genome-evaluations/sec", "value": value, "unit": "evals/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u32" if w["bits"] else "f32", "data": "synthetic",
+        "generations_per_sec": args.steps * gens / dt,
+        "config": {"workload": w["label"], "generations_per_step": gens, "seed": 42,
+                   "note": "CPU oracle (oracle/pga_oracle.c): the reference has no CPU path and its sm_20 GPU build cannot run this workload"},
+        "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(w):
+    from oracle import pyoracle as po
+    cores = os.cpu_count() or 1
+    enc = po.GENES_BITS if w["bits"] else po.GENES_F32
+    o = po.Oracle(42, threads=cores)
+    pop = o.create_population(w["size"], w["length"], enc)
+    if w.get("builtin"):
+        o.set_builtin_objective(getattr(po, "OBJ_" + w["builtin"]))
+    if w.get("hook"):
+        o.set_objective_hook(w["hook"])
+    if w.get("xover"):
+        o.set_crossover_hook(w["xover"])
+    if w.get("hook") == "tsp_obj":
+        import numpy as np
+        with open(os.path.join(ROOT, "tests", "golden", "tsp100.txt")) as f:
+            tok = f.read().split()
+        n = int(tok[0])
+        o.tsp_load(np.array(tok[1:1 + n * n], dtype=np.float32).reshape(n, n))
+    o.evaluate(pop)
+    t0 = time.perf_counter(); o.run(1); per_gen = time.perf_counter() - t0
+    gens = max(1, min(100, int(15.0 / max(per_gen, 1e-6))))
+    t0 = time.perf_counter(); o.run(gens); dt = time.perf_counter() - t0
+    o.close()
+    return {"value": gens * w["size"] / dt, "unit": "evals/s", "cores": cores, "kind": "port",
+            "sample": f"{gens} generations at full population size ({w['label']}), oracle/pga_oracle.c with OpenMP over individuals, {dt:.1f} s"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="onemax", choices=sorted(WORKLOADS))
+    ap.add_argument("--gens", type=int, default=100, help="generations per step")
+    ap.add_argument("--size", type=int, default=0, help="override the population size")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--migrate-every", type=int, default=10)
+    ap.add_argument("--migrate-pct", type=float, default=1.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    w = dict(WORKLOADS[args.workload])
+    if args.size:
+        w["size"] = args.size
+        w["label"] += f" (size overridden to {args.size})"
+
+    if args.impl == "reference":
+        run_reference_arm(args, w)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import libpga_b200 as pg
+    from libpga_b200 import islands
+
+    rank, world, local = islands.env_rank_world()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local)
+    distributed = world > 1
+    if distributed:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    enc = pg.GENES_BITS if w["bits"] else pg.GENES_F32
+    stream = torch.cuda.current_stream()
+    g = pg.PGA(seed=42)
+    g.set_stream(stream.cuda_stream)
+    if distributed:
+        islands.rendezvous(g, dist)
+        g.set_topology(pg.TOPO_RING)
+    pop = g.create_population(w["size"], w["length"], encoding=enc)
+    configure(pg, g, w)
+
+    def step():
+        if distributed:
+            g.run_islands(args.gens, args.migrate_every, args.migrate_pct)
+        else:
+            g.run(args.gens)
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    g.evaluate(pop)
+    for _ in range(args.warmup):
+        step()
+
+    # ---- value: population resident in HBM, CUDA events on the launching stream
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    launches0 = g.kernel_launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kernel_ms = 0.0
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+        kernel_ms += g.last_run_ms
+    e1.record(stream)
+    barrier()
+    elapsed_ms = e0.elapsed_time(e1)
+    launches = g.kernel_launches - launches0
+    clocks = sampler.stop()
+    if distributed:
+        t = torch.tensor([elapsed_ms, kernel_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms, kernel_ms = float(t[0]), float(t[1])
+    evals = args.steps * args.gens * w["size"] * world
+    value = evals / (elapsed_ms * 1e-3)
+
+    # ---- e2e: initial population from pinned host memory, best individual back, every step
+    host_rows = torch.empty((w["size"], pop.row_words), dtype=torch.int32, pin_memory=True)
+    host_np = host_rows.numpy().view(np.uint32 if w["bits"] else np.float32)
+    pop.genes(out=host_np)
+    h2d = host_np.nbytes
+    d2h = w["length"] * 4 + 16
+    e2e_steps = max(1, args.steps)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        pop.set_genes(host_np)          # H2D inside the call
+        step()
+        row = g.get_best(pop)           # D2H inside the call
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if distributed:
+        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t[0])
+    e2e_value = e2e_steps * (args.gens + 1) * w["size"] * world / e2e_s  # +1: the uploaded generation is scored too
+
+    peak, peak_src = measured_peak()
+    gb = genome_bytes(w)
+    n_launch = args.steps * args.gens
+    achieved = (2.0 * w["size"] * gb) / (kernel_ms * 1e-3 / n_launch) / 1e9  # algorithmic GB/s of the fused kernel
+    line = {
+        "metric": "genome-evaluations/sec", "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32" if w["bits"] else "f32", "data": "synthetic",
+        "generations_per_sec": args.steps * args.gens / (elapsed_ms * 1e-3),
+        "config": {"workload": w["label"], "generations_per_step": args.gens, "islands": world, "seed": 42,
+                   "operators": "tournament-2, uniform crossover, p=0.01 single-gene mutation",
+                   "migration": f"ring, top {args.migrate_pct}% every {args.migrate_every} generations over NCCL" if distributed else "none (single island)",
+                   "l2": "inputs larger than L2: two generations of the population = %.0f MiB vs 126 MB" % (2 * w["size"] * gb / 2 ** 20)},
+        "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": e2e_steps, "what": "upload population (pinned host) + pga_run/pga_run_islands + pga_get_best, wall clock"},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": ncu_traffic(args.workload), "kernel": "generation_fast<BITS,FUSED,ONEMAX>" if w["bits"] else "generation kernel",
+                     "algorithmic_bytes_per_launch": 2 * w["size"] * gb, "avg_launch_ms": kernel_ms / n_launch,
+                     "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0},
+    }
+    if rank == 0 and not args.no_cpu_baseline and world == 1:
+        line["cpu_baseline"] = cpu_baseline(w)
+    g.deinit()
+    if distributed:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

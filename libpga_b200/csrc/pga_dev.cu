@@ -1,0 +1,617 @@
+// pga_dev.cu -- device layer of the B200-native libpga engine (sm_100a only).
+//
+// Implements the internal C-ABI of pga_dev.h: device buffers, streams, events,
+// kernel dispatch, ranking, migration payloads and the dlopen'ed NCCL transport.
+// The host logic above it is plain C (pga_host.c).
+//
+// Data layout in HBM, per population (reference: src/pga.cu:37-46, :107-111):
+//   genes[2]  [n][stride] 32-bit words, ping-pong; stride = row words rounded up
+//             to 4 so every row is 16-byte aligned and contiguous (hooks take a
+//             contiguous float[len]; TMA bulk copies and 128-bit loads need 16 B)
+//   score[2]  [n] float, ping-pong (the fused kernel reads the parents' scores
+//             and writes the children's)
+//   best[4]   ring of 64-bit (order key, ~index) maxima, one slot per scoring launch
+// The reference's third full-size buffer, rand[n][len], does not exist here.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/pga_b200.h"
+#include "pga_dev.h"
+#include "pga_kernels.cuh"
+
+using namespace pgak;
+
+// libpga's error convention (src/pga.cu:25-33)
+#define CCE(ans) gpu_assert((ans), __FILE__, __LINE__)
+static inline void gpu_assert(cudaError_t code, const char* file, int line)
+{
+    if (code != cudaSuccess) {
+        fprintf(stderr, "GPUassert: %s %s %d\n", cudaGetErrorString(code), file, line);
+        exit((int)code);
+    }
+}
+
+struct pgadev_ctx {
+    int device;
+    int sm_count;
+    cudaStream_t own_stream, stream, side;
+    cudaEvent_t ev_main, ev_side, t0, t1;
+    unsigned long long launches;
+    ncclComm_t comm;
+    int hook_threads;  // $PGA_HOOK_THREADS override, 0 = automatic
+};
+
+struct pgadev_pop {
+    uint64_t n;
+    uint32_t len;
+    int enc;
+    uint32_t row_words;  // host-visible words per row
+    uint32_t stride;     // device words per row (multiple of 4)
+    uint32_t group;      // lanes per child on the fast path
+    uint32_t* genes[2];
+    float* score[2];
+    int gidx, sidx;
+    unsigned long long* best;
+    uint32_t best_seq;
+    int32_t* sel;
+    int capture;
+    // ranking scratch
+    TopkState* topk;
+    uint32_t *blk_gt, *blk_eq;
+    uint32_t nb;
+    uint32_t* idx[2];
+    uint64_t idx_cap[2];
+    // migration boxes
+    uint32_t *outbox, *inbox;
+    uint64_t box_cap;
+};
+
+#define LAUNCH_CHECK(ctx)              \
+    do {                               \
+        CCE(cudaPeekAtLastError());    \
+        (ctx)->launches += 1;          \
+    } while (0)
+
+static uint32_t grid_for(uint64_t work_items, uint32_t per_block, uint32_t cap)
+{
+    uint64_t g = (work_items + per_block - 1) / per_block;
+    if (g < 1) g = 1;
+    if (g > cap) g = cap;
+    return (uint32_t)g;
+}
+
+// ---- context ------------------------------------------------------------------
+
+extern "C" pgadev_ctx* pgadev_ctx_create(void)
+{
+    pgadev_ctx* c = (pgadev_ctx*)calloc(1, sizeof(*c));
+    if (!c) return NULL;
+    CCE(cudaGetDevice(&c->device));
+    cudaDeviceProp prop;
+    CCE(cudaGetDeviceProperties(&prop, c->device));
+    c->sm_count = prop.multiProcessorCount;
+    CCE(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    CCE(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    c->stream = c->own_stream;
+    CCE(cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming));
+    CCE(cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming));
+    CCE(cudaEventCreate(&c->t0));
+    CCE(cudaEventCreate(&c->t1));
+    const char* ht = getenv("PGA_HOOK_THREADS");
+    c->hook_threads = ht ? atoi(ht) : 0;
+    const char* stack = getenv("PGA_STACK_BYTES");  // device stack for deep user hooks
+    if (stack && atoi(stack) > 0) CCE(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(stack)));
+    return c;
+}
+
+static void nccl_destroy(pgadev_ctx* c);
+
+extern "C" void pgadev_ctx_destroy(pgadev_ctx* c)
+{
+    if (!c) return;
+    nccl_destroy(c);
+    CCE(cudaEventDestroy(c->ev_main));
+    CCE(cudaEventDestroy(c->ev_side));
+    CCE(cudaEventDestroy(c->t0));
+    CCE(cudaEventDestroy(c->t1));
+    CCE(cudaStreamDestroy(c->own_stream));
+    CCE(cudaStreamDestroy(c->side));
+    free(c);
+}
+
+extern "C" void pgadev_ctx_set_stream(pgadev_ctx* c, void* s) { c->stream = s ? (cudaStream_t)s : c->own_stream; }
+
+extern "C" void pgadev_ctx_sync(pgadev_ctx* c)
+{
+    CCE(cudaStreamSynchronize(c->stream));
+    CCE(cudaStreamSynchronize(c->side));
+}
+
+extern "C" unsigned long long pgadev_ctx_launches(pgadev_ctx* c) { return c->launches; }
+extern "C" void pgadev_timer_start(pgadev_ctx* c) { CCE(cudaEventRecord(c->t0, c->stream)); }
+extern "C" void pgadev_timer_stop(pgadev_ctx* c) { CCE(cudaEventRecord(c->t1, c->stream)); }
+extern "C" float pgadev_timer_ms(pgadev_ctx* c)
+{
+    float ms = 0.f;
+    CCE(cudaEventSynchronize(c->t1));
+    CCE(cudaEventElapsedTime(&ms, c->t0, c->t1));
+    return ms;
+}
+
+// ---- populations ------------------------------------------------------------------
+
+extern "C" pgadev_pop* pgadev_pop_create(pgadev_ctx* c, uint64_t size, uint32_t genome_len, int encoding)
+{
+    pgadev_pop* p = (pgadev_pop*)calloc(1, sizeof(*p));
+    if (!p) return NULL;
+    p->n = size;
+    p->len = genome_len;
+    p->enc = encoding;
+    p->row_words = encoding == PGAX_GENES_BITS ? (genome_len + 31u) / 32u : genome_len;
+    p->stride = (p->row_words + 3u) & ~3u;
+    const uint32_t nblk = p->stride >> 2;
+    p->group = 1;
+    while (p->group < nblk && p->group < 32u) p->group <<= 1;
+    const size_t gene_bytes = (size_t)(size ? size : 1) * p->stride * 4u;
+    const size_t score_bytes = (size_t)(size ? size : 1) * sizeof(float);
+    // reference: four cudaMallocs, three of them population-sized (src/pga.cu:108-111)
+    for (int i = 0; i < 2; ++i) {
+        if (cudaMalloc((void**)&p->genes[i], gene_bytes) != cudaSuccess ||
+            cudaMalloc((void**)&p->score[i], score_bytes) != cudaSuccess) {
+            cudaGetLastError();
+            pgadev_pop_destroy(c, p);
+            return NULL;
+        }
+        CCE(cudaMemsetAsync(p->score[i], 0, score_bytes, c->stream));
+    }
+    CCE(cudaMalloc((void**)&p->best, 4 * sizeof(unsigned long long)));
+    CCE(cudaMemsetAsync(p->best, 0, 4 * sizeof(unsigned long long), c->stream));
+    return p;
+}
+
+extern "C" void pgadev_pop_destroy(pgadev_ctx* c, pgadev_pop* p)
+{
+    (void)c;
+    if (!p) return;
+    for (int i = 0; i < 2; ++i) {
+        if (p->genes[i]) CCE(cudaFree(p->genes[i]));
+        if (p->score[i]) CCE(cudaFree(p->score[i]));
+        if (p->idx[i]) CCE(cudaFree(p->idx[i]));
+    }
+    if (p->best) CCE(cudaFree(p->best));
+    if (p->sel) CCE(cudaFree(p->sel));
+    if (p->topk) CCE(cudaFree(p->topk));
+    if (p->blk_gt) CCE(cudaFree(p->blk_gt));
+    if (p->blk_eq) CCE(cudaFree(p->blk_eq));
+    if (p->outbox) CCE(cudaFree(p->outbox));
+    if (p->inbox) CCE(cudaFree(p->inbox));
+    free(p);
+}
+
+extern "C" uint32_t pgadev_pop_row_words(pgadev_pop* p) { return p->row_words; }
+
+static DrawCtx make_draw(uint64_t seed, uint32_t island, uint32_t epoch)
+{
+    DrawCtx d;
+    d.k0 = (uint32_t)seed;
+    d.k1 = (uint32_t)(seed >> 32);
+    d.epoch = epoch;
+    d.island = island;
+    return d;
+}
+
+extern "C" void pgadev_pop_init_random(pgadev_ctx* c, pgadev_pop* p, uint64_t seed, uint32_t island)
+{
+    if (p->n == 0) return;
+    const uint64_t blocks16 = p->n * (p->stride >> 2);
+    const uint32_t grid = grid_for(blocks16, 256, (uint32_t)c->sm_count * 16u);
+    const DrawCtx d = make_draw(seed, island, 0);
+    if (p->enc == PGAX_GENES_BITS)
+        init_population<ENC_BITS><<<grid, 256, 0, c->stream>>>(p->genes[p->gidx], (uint32_t)p->n, p->len, p->stride, d);
+    else
+        init_population<ENC_F32><<<grid, 256, 0, c->stream>>>(p->genes[p->gidx], (uint32_t)p->n, p->len, p->stride, d);
+    LAUNCH_CHECK(c);
+}
+
+extern "C" void pgadev_pop_capture_selection(pgadev_ctx* c, pgadev_pop* p, int enable)
+{
+    (void)c;
+    if (enable && !p->sel) CCE(cudaMalloc((void**)&p->sel, (size_t)(p->n ? p->n : 1) * 2 * sizeof(int32_t)));
+    p->capture = enable;
+}
+
+extern "C" void pgadev_swap_genes(pgadev_pop* p) { p->gidx ^= 1; }
+extern "C" void pgadev_swap_scores(pgadev_pop* p) { p->sidx ^= 1; }
+
+// ---- kernel dispatch ----------------------------------------------------------------
+
+#define SMEM_LIMIT (227u * 1024u)
+
+template <uint32_t PH>
+static int launch_hooks(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+{
+    const bool want_rand = ((PH & PH_CROSSOVER) && a.xov) || ((PH & PH_MUTATE) && a.mut);
+    const uint32_t rows = 1u + ((PH & PH_CROSSOVER) ? 2u : 0u) + (want_rand ? 1u : 0u);
+    const size_t per_thread = (size_t)rows * p->stride * 4u;
+    const size_t limit = SMEM_LIMIT - 64;  // static shared memory of the kernel
+    uint32_t T = 128;
+    while (T > 32 && 128 + T * per_thread > limit) T >>= 1;
+    if (128 + T * per_thread > limit) return PGAX_ERANGE;
+    if (c->hook_threads == 32 || c->hook_threads == 64 || c->hook_threads == 128) {
+        if ((uint32_t)c->hook_threads < T) T = (uint32_t)c->hook_threads;
+    } else {
+        // enough blocks to give every SM two, when the population allows it
+        while (T > 32 && (p->n + T - 1) / T < 2ull * (uint64_t)c->sm_count) T >>= 1;
+    }
+    const size_t smem_final = 128 + T * per_thread;
+    CCE(cudaFuncSetAttribute(generation_hooks<PH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_final));
+    const uint32_t grid = (uint32_t)((p->n + T - 1) / T);
+    generation_hooks<PH><<<grid, T, smem_final, c->stream>>>(a);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+template <int ENC, uint32_t PH, int OBJ>
+static int launch_fast_inst(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+{
+    const uint32_t grid = grid_for(p->n, 256, (uint32_t)c->sm_count * 16u);
+    generation_fast<ENC, PH, OBJ><<<grid, 256, 0, c->stream>>>(a);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+template <int ENC, int OBJ>
+static int launch_fast_ph(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a, uint32_t ph)
+{
+    switch (ph) {
+        case PH_FUSED: return launch_fast_inst<ENC, PH_FUSED, OBJ>(c, p, a);
+        case PH_EVALUATE: return launch_fast_inst<ENC, PH_EVALUATE, OBJ>(c, p, a);
+        case PH_CROSSOVER: return launch_fast_inst<ENC, PH_CROSSOVER, OBJ_SUM>(c, p, a);
+        case PH_MUTATE: return launch_fast_inst<ENC, PH_MUTATE, OBJ_SUM>(c, p, a);
+        default: return PGAX_EINVAL;
+    }
+}
+
+extern "C" int pgadev_launch(pgadev_ctx* c, pgadev_pop* p, const pgadev_step* st)
+{
+    if (p->n == 0) return 0;
+    const uint32_t ph = st->phases;
+    if (ph != PH_FUSED && ph != PH_EVALUATE && ph != PH_CROSSOVER && ph != PH_MUTATE) return PGAX_EINVAL;
+
+    GenArgs a;
+    memset(&a, 0, sizeof(a));
+    a.cur = p->genes[p->gidx];
+    a.nxt = p->genes[p->gidx ^ 1];
+    a.score_in = p->score[p->sidx];
+    a.score_out = ph == PH_FUSED ? p->score[p->sidx ^ 1] : p->score[p->sidx];
+    a.best = p->best;
+    a.best_slot = p->best_seq & 3u;
+    a.sel = p->capture ? p->sel : nullptr;
+    a.n = (uint32_t)p->n;
+    a.nf = (float)p->n;
+    a.len = p->len;
+    a.lenf = (float)p->len;
+    a.stride = p->stride;
+    a.group = p->group;
+    a.draw = make_draw(st->seed, st->island, st->epoch);
+    a.objective = st->objective;
+    a.obj = (obj_fn)st->obj_hook;
+    a.mut = (mutate_fn)st->mutate_hook;
+    a.xov = (crossover_fn)st->crossover_hook;
+
+    const bool uses_xov = (ph & PH_CROSSOVER) && a.xov, uses_mut = (ph & PH_MUTATE) && a.mut;
+    const bool scores = (ph & PH_EVALUATE) != 0;
+    int rc;
+    if (p->enc == PGAX_GENES_BITS) {
+        // packed bits: default operators and the bit objective only
+        if (uses_xov || uses_mut) return PGAX_ENOSYS;
+        if (scores && st->objective != PGAX_OBJ_ONEMAX) return PGAX_ENOSYS;
+        rc = launch_fast_ph<ENC_BITS, OBJ_ONEMAX>(c, p, a, ph);
+    } else {
+        if (scores && st->objective == PGAX_OBJ_ONEMAX) return PGAX_ENOSYS;
+        const bool hook_obj = scores && st->objective == PGAX_OBJ_HOOK;
+        if (uses_xov || uses_mut || hook_obj) {
+            if (hook_obj && !a.obj) return PGAX_EINVAL;
+            switch (ph) {
+                case PH_FUSED: rc = launch_hooks<PH_FUSED>(c, p, a); break;
+                case PH_EVALUATE: rc = launch_hooks<PH_EVALUATE>(c, p, a); break;
+                case PH_CROSSOVER: rc = launch_hooks<PH_CROSSOVER>(c, p, a); break;
+                default: rc = launch_hooks<PH_MUTATE>(c, p, a); break;
+            }
+        } else {
+            switch (scores ? st->objective : PGAX_OBJ_SUM) {
+                case PGAX_OBJ_SUM: rc = launch_fast_ph<ENC_F32, OBJ_SUM>(c, p, a, ph); break;
+                case PGAX_OBJ_RASTRIGIN: rc = launch_fast_ph<ENC_F32, OBJ_RASTRIGIN>(c, p, a, ph); break;
+                case PGAX_OBJ_SPHERE: rc = launch_fast_ph<ENC_F32, OBJ_SPHERE>(c, p, a, ph); break;
+                default: return PGAX_EINVAL;
+            }
+        }
+    }
+    if (rc == 0 && scores) p->best_seq += 1;
+    return rc;
+}
+
+// ---- best individual ---------------------------------------------------------------------
+
+extern "C" void pgadev_best(pgadev_ctx* c, pgadev_pop* p, int reduced_in_kernel, uint64_t* index, float* score)
+{
+    if (!reduced_in_kernel) {
+        const uint32_t grid = grid_for(p->n, 256 * 8, (uint32_t)c->sm_count * 8u);
+        reduce_best<<<grid, 256, 0, c->stream>>>(p->score[p->sidx], (uint32_t)p->n, p->best, p->best_seq & 3u);
+        LAUNCH_CHECK(c);
+        p->best_seq += 1;
+    }
+    unsigned long long key = 0;
+    float first = 0.f;
+    CCE(cudaMemcpyAsync(&key, p->best + ((p->best_seq - 1u) & 3u), sizeof(key), cudaMemcpyDeviceToHost, c->stream));
+    CCE(cudaMemcpyAsync(&first, p->score[p->sidx], sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CCE(cudaStreamSynchronize(c->stream));
+    // src/pga.cu:221-229 never displaces a NaN sitting at index 0
+    uint64_t idx = first != first ? 0u : (uint64_t)(0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull));
+    float s = first;
+    if (idx != 0) {
+        CCE(cudaMemcpyAsync(&s, p->score[p->sidx] + idx, sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+        CCE(cudaStreamSynchronize(c->stream));
+    }
+    *index = idx;
+    *score = s;
+}
+
+// ---- host <-> device copies -----------------------------------------------------------------
+
+static void copy_rows(pgadev_ctx* c, pgadev_pop* p, uint32_t* dev_rows, void* host, bool upload)
+{
+    if (p->n == 0) return;
+    const size_t host_bytes = (size_t)p->n * p->row_words * 4u;
+    if (p->row_words == p->stride) {
+        if (upload) CCE(cudaMemcpyAsync(dev_rows, host, host_bytes, cudaMemcpyHostToDevice, c->stream));
+        else CCE(cudaMemcpyAsync(host, dev_rows, host_bytes, cudaMemcpyDeviceToHost, c->stream));
+        CCE(cudaStreamSynchronize(c->stream));
+        return;
+    }
+    uint32_t* tmp;
+    CCE(cudaMalloc((void**)&tmp, host_bytes));
+    const uint32_t grid = grid_for(p->n * p->stride, 256, (uint32_t)c->sm_count * 16u);
+    if (upload) {
+        CCE(cudaMemcpyAsync(tmp, host, host_bytes, cudaMemcpyHostToDevice, c->stream));
+        repack_rows<<<grid, 256, 0, c->stream>>>(tmp, dev_rows, p->n, p->row_words, p->stride);
+        LAUNCH_CHECK(c);
+    } else {
+        repack_rows<<<grid, 256, 0, c->stream>>>(dev_rows, tmp, p->n, p->stride, p->row_words);
+        LAUNCH_CHECK(c);
+        CCE(cudaMemcpyAsync(host, tmp, host_bytes, cudaMemcpyDeviceToHost, c->stream));
+    }
+    CCE(cudaStreamSynchronize(c->stream));
+    CCE(cudaFree(tmp));
+}
+
+extern "C" void pgadev_upload_rows(pgadev_ctx* c, pgadev_pop* p, const void* host, int next_gen)
+{
+    copy_rows(c, p, p->genes[p->gidx ^ (next_gen ? 1 : 0)], (void*)host, true);
+}
+
+extern "C" void pgadev_download_rows(pgadev_ctx* c, pgadev_pop* p, void* host, int next_gen)
+{
+    copy_rows(c, p, p->genes[p->gidx ^ (next_gen ? 1 : 0)], host, false);
+}
+
+extern "C" void pgadev_download_row(pgadev_ctx* c, pgadev_pop* p, uint64_t index, void* host_words)
+{
+    CCE(cudaMemcpyAsync(host_words, p->genes[p->gidx] + index * p->stride, (size_t)p->row_words * 4u, cudaMemcpyDeviceToHost,
+                        c->stream));
+    CCE(cudaStreamSynchronize(c->stream));
+}
+
+extern "C" void pgadev_upload_scores(pgadev_ctx* c, pgadev_pop* p, const float* host)
+{
+    CCE(cudaMemcpyAsync(p->score[p->sidx], host, p->n * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    CCE(cudaStreamSynchronize(c->stream));
+}
+
+extern "C" void pgadev_download_scores(pgadev_ctx* c, pgadev_pop* p, float* host)
+{
+    CCE(cudaMemcpyAsync(host, p->score[p->sidx], p->n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CCE(cudaStreamSynchronize(c->stream));
+}
+
+extern "C" int pgadev_download_selection(pgadev_ctx* c, pgadev_pop* p, int32_t* host_pairs)
+{
+    if (!p->sel) return PGAX_EINVAL;
+    CCE(cudaMemcpyAsync(host_pairs, p->sel, p->n * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    CCE(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// ---- ranking ------------------------------------------------------------------------------
+
+static void ensure_index_list(pgadev_ctx* c, pgadev_pop* p, int slot, uint64_t k)
+{
+    if (p->idx_cap[slot] >= k) return;
+    pgadev_ctx_sync(c);
+    if (p->idx[slot]) CCE(cudaFree(p->idx[slot]));
+    CCE(cudaMalloc((void**)&p->idx[slot], k * sizeof(uint32_t)));
+    p->idx_cap[slot] = k;
+}
+
+extern "C" void pgadev_select_top(pgadev_ctx* c, pgadev_pop* p, uint64_t k, int worst, int slot)
+{
+    if (k == 0 || p->n == 0) return;
+    if (k > p->n) k = p->n;
+    if (!p->topk) {
+        p->nb = (uint32_t)((p->n + TOPK_CHUNK - 1) / TOPK_CHUNK);
+        CCE(cudaMalloc((void**)&p->topk, sizeof(TopkState)));
+        CCE(cudaMalloc((void**)&p->blk_gt, (size_t)p->nb * sizeof(uint32_t)));
+        CCE(cudaMalloc((void**)&p->blk_eq, (size_t)p->nb * sizeof(uint32_t)));
+    }
+    ensure_index_list(c, p, slot, k);
+    const float* score = p->score[p->sidx];
+    const uint32_t n = (uint32_t)p->n;
+    topk_begin<<<1, 256, 0, c->stream>>>(p->topk, (uint32_t)k);
+    LAUNCH_CHECK(c);
+    const uint32_t hgrid = grid_for(p->n, 256, (uint32_t)c->sm_count * 8u);
+    for (int pass = 3; pass >= 0; --pass) {
+        topk_histogram<<<hgrid, 256, 0, c->stream>>>(score, n, worst, (uint32_t)pass * 8u, p->topk);
+        LAUNCH_CHECK(c);
+        topk_pick<<<1, 256, 0, c->stream>>>(p->topk, (uint32_t)pass * 8u);
+        LAUNCH_CHECK(c);
+    }
+    topk_count<<<p->nb, TOPK_BLOCK, 0, c->stream>>>(score, n, worst, p->topk, p->blk_gt, p->blk_eq);
+    LAUNCH_CHECK(c);
+    topk_scan<<<1, 1024, 0, c->stream>>>(p->blk_gt, p->blk_eq, p->nb);
+    LAUNCH_CHECK(c);
+    topk_emit<<<p->nb, TOPK_BLOCK, 0, c->stream>>>(score, n, worst, p->topk, p->blk_gt, p->blk_eq, p->idx[slot]);
+    LAUNCH_CHECK(c);
+}
+
+extern "C" void pgadev_download_top(pgadev_ctx* c, pgadev_pop* p, int slot, uint64_t k, uint32_t* host_idx)
+{
+    CCE(cudaMemcpyAsync(host_idx, p->idx[slot], k * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    CCE(cudaStreamSynchronize(c->stream));
+}
+
+// ---- migration payloads -----------------------------------------------------------------------
+
+static void ensure_boxes(pgadev_ctx* c, pgadev_pop* p, uint64_t k)
+{
+    if (p->box_cap >= k) return;
+    pgadev_ctx_sync(c);
+    if (p->outbox) CCE(cudaFree(p->outbox));
+    if (p->inbox) CCE(cudaFree(p->inbox));
+    const size_t bytes = (size_t)k * (p->stride + 1u) * 4u;
+    CCE(cudaMalloc((void**)&p->outbox, bytes));
+    CCE(cudaMalloc((void**)&p->inbox, bytes));
+    p->box_cap = k;
+}
+
+static size_t box_words(const pgadev_pop* p, uint64_t k) { return (size_t)k * (p->stride + 1u); }
+
+extern "C" void pgadev_reserve_boxes(pgadev_ctx* c, pgadev_pop* p, uint64_t k) { ensure_boxes(c, p, k); }
+
+extern "C" void pgadev_pack_emigrants(pgadev_ctx* c, pgadev_pop* p, uint64_t k)
+{
+    ensure_boxes(c, p, k);
+    const uint32_t grid = grid_for(k * (p->stride >> 2), 256, (uint32_t)c->sm_count * 8u);
+    pack_rows<<<grid, 256, 0, c->stream>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[0], (uint32_t)k, p->stride, p->outbox);
+    LAUNCH_CHECK(c);
+}
+
+extern "C" void pgadev_transfer_local(pgadev_ctx* c, pgadev_pop* src, pgadev_pop* dst, uint64_t k)
+{
+    CCE(cudaMemcpyAsync(dst->inbox, src->outbox, box_words(src, k) * 4u, cudaMemcpyDeviceToDevice, c->side));
+}
+
+extern "C" void pgadev_unpack_immigrants(pgadev_ctx* c, pgadev_pop* p, uint64_t k)
+{
+    const uint32_t grid = grid_for(k * (p->stride >> 2), 256, (uint32_t)c->sm_count * 8u);
+    unpack_rows<<<grid, 256, 0, c->stream>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[1], (uint32_t)k, p->stride, p->inbox);
+    LAUNCH_CHECK(c);
+}
+
+extern "C" void pgadev_side_after_main(pgadev_ctx* c)
+{
+    CCE(cudaEventRecord(c->ev_main, c->stream));
+    CCE(cudaStreamWaitEvent(c->side, c->ev_main, 0));
+}
+
+extern "C" void pgadev_main_after_side(pgadev_ctx* c)
+{
+    CCE(cudaEventRecord(c->ev_side, c->side));
+    CCE(cudaStreamWaitEvent(c->stream, c->ev_side, 0));
+}
+
+// ---- NCCL, loaded on demand ----------------------------------------------------------------------
+// The reference's link line is "-lpga -lcurand" (test/Makefile:3): nothing may add
+// -lnccl to it, so the transport is resolved with dlopen the first time a
+// multi-process island layout asks for it.
+
+struct nccl_api {
+    void* handle;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*);
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
+    ncclResult_t (*CommDestroy)(ncclComm_t);
+    ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    ncclResult_t (*GroupStart)(void);
+    ncclResult_t (*GroupEnd)(void);
+    const char* (*GetErrorString)(ncclResult_t);
+};
+static nccl_api g_nccl;
+
+static int nccl_load(void)
+{
+    if (g_nccl.handle) return 0;
+    const char* names[] = { getenv("PGA_NCCL_LIB"), "libnccl.so.2", "libnccl.so" };
+    void* h = NULL;
+    for (int i = 0; i < 3 && !h; ++i)
+        if (names[i] && *names[i]) h = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return PGAX_ENCCL;
+#define SYM(field, name)                                  \
+    *(void**)(&g_nccl.field) = dlsym(h, name);            \
+    if (!g_nccl.field) { dlclose(h); return PGAX_ENCCL; }
+    SYM(GetUniqueId, "ncclGetUniqueId")
+    SYM(CommInitRank, "ncclCommInitRank")
+    SYM(CommDestroy, "ncclCommDestroy")
+    SYM(Send, "ncclSend")
+    SYM(Recv, "ncclRecv")
+    SYM(GroupStart, "ncclGroupStart")
+    SYM(GroupEnd, "ncclGroupEnd")
+    SYM(GetErrorString, "ncclGetErrorString")
+#undef SYM
+    g_nccl.handle = h;
+    return 0;
+}
+
+#define NCE(ans) nccl_assert((ans), __FILE__, __LINE__)
+static inline void nccl_assert(ncclResult_t r, const char* file, int line)
+{
+    if (r != ncclSuccess) {
+        fprintf(stderr, "GPUassert: NCCL %s %s %d\n", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "error", file, line);
+        exit((int)r);
+    }
+}
+
+static void nccl_destroy(pgadev_ctx* c)
+{
+    if (c->comm && g_nccl.handle) g_nccl.CommDestroy(c->comm);
+    c->comm = NULL;
+}
+
+extern "C" int pgadev_nccl_unique_id(void* out128)
+{
+    if (!out128) return PGAX_EINVAL;
+    if (nccl_load() != 0) return PGAX_ENCCL;
+    ncclUniqueId id;
+    static_assert(sizeof(ncclUniqueId) == PGAX_UNIQUE_ID_BYTES, "ncclUniqueId size");
+    NCE(g_nccl.GetUniqueId(&id));
+    memcpy(out128, &id, sizeof(id));
+    return 0;
+}
+
+extern "C" int pgadev_nccl_init(pgadev_ctx* c, int rank, int world, const void* id128)
+{
+    if (!id128) return PGAX_EINVAL;
+    if (nccl_load() != 0) return PGAX_ENCCL;
+    ncclUniqueId id;
+    memcpy(&id, id128, sizeof(id));
+    nccl_destroy(c);
+    CCE(cudaSetDevice(c->device));
+    NCE(g_nccl.CommInitRank(&c->comm, world, id, rank));
+    return 0;
+}
+
+extern "C" void pgadev_nccl_group_begin(pgadev_ctx* c) { (void)c; NCE(g_nccl.GroupStart()); }
+extern "C" void pgadev_nccl_group_end(pgadev_ctx* c) { (void)c; NCE(g_nccl.GroupEnd()); }
+
+extern "C" void pgadev_nccl_send_outbox(pgadev_ctx* c, pgadev_pop* src, uint64_t k, int peer)
+{
+    NCE(g_nccl.Send(src->outbox, box_words(src, k), ncclUint32, peer, c->comm, c->side));
+}
+
+extern "C" void pgadev_nccl_recv_inbox(pgadev_ctx* c, pgadev_pop* dst, uint64_t k, int peer)
+{
+    NCE(g_nccl.Recv(dst->inbox, box_words(dst, k), ncclUint32, peer, c->comm, c->side));
+}

@@ -1,0 +1,657 @@
+// pga_kernels.cuh -- the generation kernels of the B200-native libpga engine.
+//
+// One launch = one pass over a population.  With all three phases enabled it is
+// the fused generation: tournament selection, crossover, mutation, scoring of the
+// child and the best-of-population reduction, reading each parent row once and
+// writing each child row once.  It replaces the reference's four kernels and its
+// cuRAND pass (src/pga.cu:81-86, :99-101, :250-262, :294-317, :333-347) and the
+// host argmax of pga_get_best (src/pga.cu:218-236).
+//
+// Two families:
+//   generation_hooks  - user hooks are device function pointers with a serial,
+//                       one-thread-per-individual ABI (include/pga.h:46-48); rows are
+//                       staged in shared memory with TMA bulk copies and handed to
+//                       the hooks there.
+//   generation_fast   - default operators + built-in objective, no indirect calls:
+//                       a group of lanes per child, 128-bit coalesced row accesses,
+//                       everything in registers.
+#pragma once
+
+#include "pga_device_utils.cuh"
+
+namespace pgak {
+
+typedef float (*obj_fn)(float*, unsigned);
+typedef void (*mutate_fn)(float*, float*, unsigned);
+typedef void (*crossover_fn)(float*, float*, float*, float*, unsigned);
+
+enum : uint32_t { PH_CROSSOVER = 1u, PH_MUTATE = 2u, PH_EVALUATE = 4u, PH_FUSED = 7u };
+enum : int { ENC_F32 = 0, ENC_BITS = 1 };
+
+#define PGA_MUTATION_CHANCE 0.01f /* src/pga.cu:128 */
+
+struct GenArgs {
+    const uint32_t* cur;    // [n][stride] current generation
+    uint32_t* nxt;          // [n][stride] next generation
+    const float* score_in;  // scores of cur (selection)
+    float* score_out;       // scores written by the EVALUATE phase
+    unsigned long long* best;  // ring of 4 best-keys
+    uint32_t best_slot;        // slot this launch reduces into
+    int32_t* sel;              // optional [n][2] capture of the tournament winners
+    uint32_t n;
+    float nf;        // (float)n, the multiplier of the index draw
+    uint32_t len;    // genes per genome (bits for ENC_BITS)
+    float lenf;      // (float)len
+    uint32_t stride; // 32-bit words per stored row, multiple of 4
+    uint32_t group;  // fast path: lanes per child (power of two <= 32)
+    DrawCtx draw;
+    int objective;
+    obj_fn obj;
+    mutate_fn mut;
+    crossover_fn xov;
+};
+
+// ---- shared pieces ----------------------------------------------------------
+
+// size-2 tournament (src/pga.cu:280-292): the second candidate wins only if
+// strictly better, so ties and NaNs keep the first
+__device__ __forceinline__ uint32_t tournament(const float* __restrict__ score, float ua, float ub, float nf, uint32_t n)
+{
+    const uint32_t a = draw_index(ua, nf, n), b = draw_index(ub, nf, n);
+    const float sa = __ldg(score + a), sb = __ldg(score + b);
+    return sa < sb ? b : a;
+}
+
+// per-block best: warp shuffles, then one atomic per block
+__device__ __forceinline__ void block_best_commit(unsigned long long key, unsigned long long* slot,
+                                                  unsigned long long* warp_scratch)
+{
+    key = warp_max_u64(key);
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31u) >> 5;
+    if (lane == 0) warp_scratch[warp] = key;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned long long k = lane < nwarps ? warp_scratch[lane] : 0ull;
+        k = warp_max_u64(k);
+        if (lane == 0 && k != 0ull) atomicMax(slot, k);
+    }
+}
+
+// ---- hook path ----------------------------------------------------------------
+//
+// Block of T threads <-> T consecutive children.  Shared memory holds, per thread,
+// the child row and (crossover phase) both parent rows, plus the rand row when a
+// hook wants one.  Parent rows arrive by one TMA bulk copy each, issued by the
+// thread that ran the tournament; the block's child rows leave by ONE bulk store,
+// because consecutive children are contiguous in next_gen.
+template <uint32_t PH>
+__global__ void __launch_bounds__(128) generation_hooks(const __grid_constant__ GenArgs a)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ unsigned long long warp_best[4];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw);
+    float* rows = reinterpret_cast<float*>(smem_raw + 128);
+
+    const uint32_t T = blockDim.x, t = threadIdx.x, lane = t & 31u, warp = t >> 5;
+    const uint32_t S = a.stride;
+    const bool want_rand = ((PH & PH_CROSSOVER) && a.xov != nullptr) || ((PH & PH_MUTATE) && a.mut != nullptr);
+
+    float* s_child = rows;
+    float* s_p1 = s_child + (size_t)T * S;
+    float* s_p2 = (PH & PH_CROSSOVER) ? s_p1 + (size_t)T * S : s_p1;
+    float* s_rnd = (PH & PH_CROSSOVER) ? s_p2 + (size_t)T * S : s_p1;
+
+    const uint32_t base = blockIdx.x * T;
+    const uint32_t nact = min(T, a.n - base);
+    const bool active = t < nact;
+    const uint32_t i = base + t;
+    const uint32_t row_bytes = S * 4u;
+
+    if (t == 0) {
+        mbar_init(bar, 1);
+        if ((PH & PH_EVALUATE) && blockIdx.x == 0) a.best[(a.best_slot + 1u) & 3u] = 0ull;
+    }
+    __syncthreads();
+
+    // draws 0..3 of the child's rand row: selection and the default mutation
+    float u0 = 0.f, u1 = 1.f, u2 = 0.f, u3 = 0.f;
+    if (active && (PH & (PH_CROSSOVER | PH_MUTATE))) {
+        const uint4 w = draw_block(a.draw, STREAM_ROW, i, 0);
+        u0 = to_uniform(w.x); u1 = to_uniform(w.y); u2 = to_uniform(w.z); u3 = to_uniform(w.w);
+    }
+
+    if (PH & PH_CROSSOVER) {
+        if (t == 0) mbar_arrive_expect_tx(bar, nact * 2u * row_bytes);
+        if (active) {
+            const uint32_t p1 = tournament(a.score_in, u0, u1, a.nf, a.n);  // src/pga.cu:306
+            const uint32_t p2 = tournament(a.score_in, u2, u3, a.nf, a.n);  // src/pga.cu:307
+            if (a.sel) { a.sel[2 * (size_t)i] = (int32_t)p1; a.sel[2 * (size_t)i + 1] = (int32_t)p2; }
+            bulk_load(s_p1 + (size_t)t * S, a.cur + (size_t)p1 * S, row_bytes, bar);
+            bulk_load(s_p2 + (size_t)t * S, a.cur + (size_t)p2 * S, row_bytes, bar);
+        }
+    } else {
+        // the block's own rows are contiguous: one copy
+        const uint32_t* src = (PH & PH_MUTATE) ? a.nxt : a.cur;
+        if (t == 0) {
+            mbar_arrive_expect_tx(bar, nact * row_bytes);
+            bulk_load(s_child, src + (size_t)base * S, nact * row_bytes, bar);
+        }
+    }
+
+    // rand rows for the hooks, generated while the copies are in flight; each warp
+    // serves its own 32 children, lanes across Philox blocks
+    if (want_rand) {
+        for (uint32_t c = 0; c < 32u; ++c) {
+            const uint32_t tt = warp * 32u + c;
+            if (tt >= nact) break;
+            for (uint32_t b = lane; b < (S >> 2); b += 32u) {
+                const uint4 w = draw_block(a.draw, STREAM_ROW, base + tt, b);
+                *reinterpret_cast<float4*>(s_rnd + (size_t)tt * S + 4u * b) =
+                    make_float4(to_uniform(w.x), to_uniform(w.y), to_uniform(w.z), to_uniform(w.w));
+            }
+        }
+    }
+
+    mbar_wait(bar, 0);
+    __syncwarp();
+
+    if (PH & PH_CROSSOVER) {
+        if (a.xov != nullptr) {
+            if (active) {
+                float* c = s_child + (size_t)t * S;
+                a.xov(s_p1 + (size_t)t * S, s_p2 + (size_t)t * S, c, s_rnd + (size_t)t * S, a.len);  // src/pga.cu:305
+                for (uint32_t j = a.len; j < S; ++j) c[j] = 0.f;
+            }
+        } else {
+            // default uniform crossover (src/pga.cu:135-143), cooperative per warp
+            for (uint32_t c = 0; c < 32u; ++c) {
+                const uint32_t tt = warp * 32u + c;
+                if (tt >= nact) break;
+                for (uint32_t b = lane; b < (S >> 2); b += 32u) {
+                    float4 r;
+                    if (want_rand) {
+                        r = *reinterpret_cast<const float4*>(s_rnd + (size_t)tt * S + 4u * b);
+                    } else {
+                        const uint4 w = draw_block(a.draw, STREAM_ROW, base + tt, b);
+                        r = make_float4(to_uniform(w.x), to_uniform(w.y), to_uniform(w.z), to_uniform(w.w));
+                    }
+                    const float4 x = *reinterpret_cast<const float4*>(s_p1 + (size_t)tt * S + 4u * b);
+                    const float4 y = *reinterpret_cast<const float4*>(s_p2 + (size_t)tt * S + 4u * b);
+                    float4 o;
+                    o.x = r.x > 0.5f ? x.x : y.x;
+                    o.y = r.y > 0.5f ? x.y : y.y;
+                    o.z = r.z > 0.5f ? x.z : y.z;
+                    o.w = r.w > 0.5f ? x.w : y.w;
+                    *reinterpret_cast<float4*>(s_child + (size_t)tt * S + 4u * b) = o;
+                }
+            }
+        }
+        __syncwarp();
+    }
+
+    if (PH & PH_MUTATE) {
+        if (active) {
+            float* c = s_child + (size_t)t * S;
+            if (a.mut != nullptr) {
+                a.mut(c, s_rnd + (size_t)t * S, a.len);  // src/pga.cu:341
+            } else if (u1 <= PGA_MUTATION_CHANCE) {      // src/pga.cu:127-133
+                c[draw_index(u0, a.lenf, a.len)] = u2;
+            }
+        }
+        __syncwarp();
+    }
+
+    if (PH & PH_EVALUATE) {
+        unsigned long long key = 0ull;
+        if (active) {
+            float* c = s_child + (size_t)t * S;
+            const float s = a.objective == OBJ_HOOK ? a.obj(c, a.len) : objective_serial(a.objective, c, a.len);  // src/pga.cu:258
+            a.score_out[i] = s;
+            key = best_key(s, i);
+        }
+        block_best_commit(key, a.best + a.best_slot, warp_best);
+    }
+
+    if (PH & (PH_CROSSOVER | PH_MUTATE)) {
+        fence_async_smem();
+        __syncthreads();
+        if (t == 0) {
+            bulk_store(a.nxt + (size_t)base * S, s_child, nact * row_bytes);
+            bulk_store_commit_and_wait();
+        }
+    }
+}
+
+// ---- fast path ------------------------------------------------------------------
+//
+// A warp takes 32 consecutive children per iteration.  Lane j runs the
+// tournaments of child base+j (four independent score gathers in flight per
+// lane).  The rows are then processed in G tiles of 32/G children: a group of G
+// lanes owns one child and walks its 16-byte blocks gl, gl+G, ... with 128-bit
+// loads from both parents and a 128-bit store of the child; consecutive groups
+// write consecutive rows, so a tile's stores are one contiguous span.
+//
+// f32 scores follow the oracle's canonical reduction (lane gl accumulates its
+// blocks in order, xor butterfly over the group) and are therefore bit-exact.
+template <int ENC, uint32_t PH, int OBJ>
+__global__ void __launch_bounds__(256) generation_fast(const __grid_constant__ GenArgs a)
+{
+    __shared__ unsigned long long warp_best[8];
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t S = a.stride, nblk = S >> 2;
+    const uint32_t G = a.group, cpt = 32u / G;
+    const uint32_t gl = lane & (G - 1u), grp = lane / G;
+    const uint4* __restrict__ cur = reinterpret_cast<const uint4*>(a.cur);
+    uint4* __restrict__ nxt = reinterpret_cast<uint4*>(a.nxt);
+
+    if ((PH & PH_EVALUATE) && blockIdx.x == 0 && threadIdx.x == 0) a.best[(a.best_slot + 1u) & 3u] = 0ull;
+
+    unsigned long long key = 0ull;
+
+    for (uint64_t cbase64 = (uint64_t)gwarp * 32u; cbase64 < a.n; cbase64 += (uint64_t)nwarps * 32u) {
+        const uint32_t cbase = (uint32_t)cbase64;
+        const uint32_t mine = cbase + lane;
+        const bool have = mine < a.n;
+
+        uint32_t p1 = 0, p2 = 0, m_idx = 0, m_val = 0;
+        bool m_on = false;
+        if ((PH & (PH_CROSSOVER | PH_MUTATE)) && have) {
+            const uint4 w = draw_block(a.draw, STREAM_ROW, mine, 0);
+            const float u0 = to_uniform(w.x), u1 = to_uniform(w.y), u2 = to_uniform(w.z), u3 = to_uniform(w.w);
+            if (PH & PH_CROSSOVER) {
+                p1 = tournament(a.score_in, u0, u1, a.nf, a.n);
+                p2 = tournament(a.score_in, u2, u3, a.nf, a.n);
+                if (a.sel) { a.sel[2 * (size_t)mine] = (int32_t)p1; a.sel[2 * (size_t)mine + 1] = (int32_t)p2; }
+            }
+            if (PH & PH_MUTATE) {
+                m_on = u1 <= PGA_MUTATION_CHANCE;
+                m_idx = draw_index(u0, a.lenf, a.len);
+                m_val = ENC == ENC_BITS ? (u2 > 0.5f ? 1u : 0u) : __float_as_uint(u2);
+            }
+        }
+
+        float my_score = 0.f;
+        for (uint32_t tile = 0; tile < G; ++tile) {
+            const uint32_t src_lane = tile * cpt + grp;
+            const uint32_t child = cbase + src_lane;
+            const bool valid = child < a.n;
+            const uint32_t q1 = __shfl_sync(0xFFFFFFFFu, p1, src_lane);
+            const uint32_t q2 = __shfl_sync(0xFFFFFFFFu, p2, src_lane);
+            const bool c_on = __shfl_sync(0xFFFFFFFFu, (int)m_on, src_lane) != 0;
+            const uint32_t c_idx = __shfl_sync(0xFFFFFFFFu, m_idx, src_lane);
+            const uint32_t c_val = __shfl_sync(0xFFFFFFFFu, m_val, src_lane);
+            // the 16-byte block that holds the mutated gene
+            const uint32_t c_blk = ENC == ENC_BITS ? (c_idx >> 7) : (c_idx >> 2);
+
+            float facc = 0.f;
+            uint32_t iacc = 0;
+            if (valid) {
+                for (uint32_t b = gl; b < nblk; b += G) {
+                    uint4 c;
+                    if (PH & PH_CROSSOVER) {
+                        const uint4 x = __ldg(cur + (size_t)q1 * nblk + b);
+                        const uint4 y = __ldg(cur + (size_t)q2 * nblk + b);
+                        if (ENC == ENC_BITS) {
+                            const uint4 m = draw_block(a.draw, STREAM_MASK, child, b);
+                            c.x = (x.x & m.x) | (y.x & ~m.x);
+                            c.y = (x.y & m.y) | (y.y & ~m.y);
+                            c.z = (x.z & m.z) | (y.z & ~m.z);
+                            c.w = (x.w & m.w) | (y.w & ~m.w);
+                        } else {
+                            const uint4 w = draw_block(a.draw, STREAM_ROW, child, b);
+                            c.x = to_uniform(w.x) > 0.5f ? x.x : y.x;  // src/pga.cu:137-141
+                            c.y = to_uniform(w.y) > 0.5f ? x.y : y.y;
+                            c.z = to_uniform(w.z) > 0.5f ? x.z : y.z;
+                            c.w = to_uniform(w.w) > 0.5f ? x.w : y.w;
+                        }
+                    } else {
+                        // a pass without crossover works on the row itself: the mutate
+                        // step edits next_gen in place, the evaluate step reads current_gen
+                        c = (PH & PH_MUTATE) ? nxt[(size_t)child * nblk + b] : __ldg(cur + (size_t)child * nblk + b);
+                    }
+                    bool touched = false;
+                    if ((PH & PH_MUTATE) && c_on && c_blk == b) {  // src/pga.cu:127-133
+                        touched = true;
+                        if (ENC == ENC_BITS) {
+                            const uint32_t word = (c_idx >> 5) & 3u, bit = 1u << (c_idx & 31u);
+                            uint32_t* cw = word == 0 ? &c.x : word == 1 ? &c.y : word == 2 ? &c.z : &c.w;
+                            *cw = c_val ? (*cw | bit) : (*cw & ~bit);
+                        } else {
+                            const uint32_t e = c_idx & 3u;
+                            if (e == 0) c.x = c_val; else if (e == 1) c.y = c_val; else if (e == 2) c.z = c_val; else c.w = c_val;
+                        }
+                    }
+                    if (PH & PH_EVALUATE) {
+                        if (ENC == ENC_BITS) {
+                            iacc += __popc(c.x) + __popc(c.y) + __popc(c.z) + __popc(c.w);
+                        } else {
+                            const uint32_t j = 4u * b;
+                            if (j + 0 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.x));
+                            if (j + 1 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.y));
+                            if (j + 2 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.z));
+                            if (j + 3 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.w));
+                        }
+                    }
+                    if (PH & PH_CROSSOVER)
+                        nxt[(size_t)child * nblk + b] = c;
+                    else if ((PH & PH_MUTATE) && touched)
+                        nxt[(size_t)child * nblk + b] = c;
+                }
+            }
+            if (PH & PH_EVALUATE) {
+                float s;
+                if (ENC == ENC_BITS) {
+                    for (uint32_t off = G >> 1; off >= 1u; off >>= 1) iacc += __shfl_xor_sync(0xFFFFFFFFu, iacc, off);
+                    s = __uint2float_rn(iacc);
+                } else {
+                    for (uint32_t off = G >> 1; off >= 1u; off >>= 1)
+                        facc = __fadd_rn(facc, __shfl_xor_sync(0xFFFFFFFFu, facc, off));
+                    s = obj_finalize<OBJ>(facc, a.len);
+                }
+                // hand the score to the lane that ran this child's tournaments
+                const float v = __shfl_sync(0xFFFFFFFFu, s, (lane % cpt) * G);
+                if (lane / cpt == tile) my_score = v;
+            }
+        }
+        if ((PH & PH_EVALUATE) && have) {
+            a.score_out[mine] = my_score;
+            const unsigned long long k = best_key(my_score, mine);
+            key = k > key ? k : key;
+        }
+    }
+    if (PH & PH_EVALUATE) block_best_commit(key, a.best + a.best_slot, warp_best);
+}
+
+// ---- population set-up (src/pga.cu:81-86, :116-117): genes := rand row of epoch 0 ----
+template <int ENC>
+__global__ void init_population(uint32_t* rows, uint32_t n, uint32_t len, uint32_t stride, DrawCtx d)
+{
+    const uint32_t nblk = stride >> 2;
+    const uint64_t total = (uint64_t)n * nblk;
+    for (uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t i = (uint32_t)(k / nblk), b = (uint32_t)(k % nblk);
+        uint4 w = draw_block(d, ENC == ENC_BITS ? STREAM_INITBITS : STREAM_ROW, i, b);
+        if (ENC == ENC_BITS) {
+            uint32_t out[4];
+            for (int q = 0; q < 4; ++q) {
+                const uint32_t lo = (4u * b + q) * 32u;  // first bit of this word
+                uint32_t v = q == 0 ? w.x : q == 1 ? w.y : q == 2 ? w.z : w.w;
+                if (lo >= len) v = 0u;
+                else if (len - lo < 32u) v &= (1u << (len - lo)) - 1u;
+                out[q] = v;
+            }
+            w = make_uint4(out[0], out[1], out[2], out[3]);
+        } else {
+            uint32_t out[4] = { w.x, w.y, w.z, w.w };
+            for (int q = 0; q < 4; ++q)
+                out[q] = (4u * b + q < len) ? __float_as_uint(to_uniform(out[q])) : 0u;
+            w = make_uint4(out[0], out[1], out[2], out[3]);
+        }
+        reinterpret_cast<uint4*>(rows)[k] = w;
+    }
+}
+
+// ---- stand-alone best reduction (after uploads and migrations) -----------------
+__global__ void __launch_bounds__(256) reduce_best(const float* __restrict__ score, uint32_t n, unsigned long long* best,
+                                                   uint32_t slot)
+{
+    __shared__ unsigned long long warp_best[8];
+    if (blockIdx.x == 0 && threadIdx.x == 0) best[(slot + 1u) & 3u] = 0ull;
+    unsigned long long key = 0ull;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const unsigned long long k = best_key(__ldg(score + i), (uint32_t)i);
+        key = k > key ? k : key;
+    }
+    block_best_commit(key, best + slot, warp_best);
+}
+
+// ---- top-k radix select ------------------------------------------------------------
+//
+// Picks the k best (or k worst) individuals under the engine's total order and
+// lists them in ascending index order.  Four 8-bit passes over the 32-bit order
+// key find the k-th key T; a stable compaction then takes every key beyond T and
+// as many keys equal to T as are still needed (lowest indices first for "best",
+// highest first for "worst").  Histogram updates are aggregated per warp with
+// __match_any_sync before they touch shared memory.
+struct TopkState {
+    uint32_t hist[256];
+    uint32_t prefix;     // digits fixed so far
+    uint32_t mask;       // which bits of `prefix` are fixed
+    uint32_t remaining;  // rank still to find inside the prefix bucket
+    uint32_t threshold;  // final: the k-th key
+    uint32_t need_eq;    // final: how many keys == threshold are taken
+    uint32_t total_eq;   // final: how many keys == threshold exist
+    uint32_t total_gt;   // final: how many keys  > threshold exist
+    uint32_t pad;
+};
+
+#define TOPK_BLOCK 256u
+#define TOPK_ROUNDS 8u
+#define TOPK_CHUNK (TOPK_BLOCK * TOPK_ROUNDS)
+
+__device__ __forceinline__ uint32_t select_key(float s, int worst)
+{
+    const uint32_t k = order_key(s);
+    return worst ? ~k : k;
+}
+
+__global__ void topk_begin(TopkState* st, uint32_t k)
+{
+    const uint32_t t = threadIdx.x;
+    if (t < 256u) st->hist[t] = 0u;
+    if (t == 0) {
+        st->prefix = 0u; st->mask = 0u; st->remaining = k;
+        st->threshold = 0u; st->need_eq = 0u; st->total_eq = 0u; st->total_gt = 0u;
+    }
+}
+
+__global__ void __launch_bounds__(256) topk_histogram(const float* __restrict__ score, uint32_t n, int worst, uint32_t shift,
+                                                      TopkState* st)
+{
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0u;
+    __syncthreads();
+    const uint32_t prefix = st->prefix, mask = st->mask;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t span = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t base = (uint64_t)blockIdx.x * blockDim.x; base < n; base += span) {
+        const uint64_t i = base + threadIdx.x;
+        const bool in = i < n;
+        uint32_t key = 0u;
+        bool hit = false;
+        if (in) {
+            key = select_key(__ldg(score + i), worst);
+            hit = (key & mask) == prefix;
+        }
+        const uint32_t digit = (key >> shift) & 255u;
+        // one shared-memory atomic per distinct digit in the warp
+        const uint32_t voters = __ballot_sync(0xFFFFFFFFu, hit);
+        if (hit) {
+            const uint32_t peers = __match_any_sync(voters, digit);
+            if ((peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&h[digit], (uint32_t)__popc(peers));
+        }
+    }
+    __syncthreads();
+    if (h[threadIdx.x]) atomicAdd(&st->hist[threadIdx.x], h[threadIdx.x]);
+}
+
+// one block: walk the digits from the top until the cumulative count reaches `remaining`
+__global__ void topk_pick(TopkState* st, uint32_t shift)
+{
+    __shared__ uint32_t h[256];
+    const uint32_t t = threadIdx.x;
+    h[t] = st->hist[t];
+    __syncthreads();
+    if (t == 0) {
+        uint32_t rem = st->remaining, above = 0u, d = 255u;
+        for (;; --d) {
+            if (above + h[d] >= rem || d == 0u) break;
+            above += h[d];
+        }
+        st->remaining = rem - above;
+        st->prefix |= d << shift;
+        st->mask |= 255u << shift;
+        st->total_gt += above;
+        if (shift == 0u) {
+            st->threshold = st->prefix;
+            st->need_eq = rem - above;
+            st->total_eq = h[d];
+        }
+    }
+    __syncthreads();
+    st->hist[t] = 0u;
+}
+
+__global__ void __launch_bounds__(256) topk_count(const float* __restrict__ score, uint32_t n, int worst, const TopkState* st,
+                                                  uint32_t* block_gt, uint32_t* block_eq)
+{
+    __shared__ uint32_t s_gt, s_eq;
+    if (threadIdx.x == 0) { s_gt = 0u; s_eq = 0u; }
+    __syncthreads();
+    const uint32_t T = st->threshold;
+    uint32_t gt = 0u, eq = 0u;
+    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
+    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+        if (i < n) {
+            const uint32_t key = select_key(__ldg(score + i), worst);
+            gt += key > T;
+            eq += key == T;
+        }
+    }
+    for (int off = 16; off >= 1; off >>= 1) {
+        gt += __shfl_xor_sync(0xFFFFFFFFu, gt, off);
+        eq += __shfl_xor_sync(0xFFFFFFFFu, eq, off);
+    }
+    if ((threadIdx.x & 31u) == 0u) { atomicAdd(&s_gt, gt); atomicAdd(&s_eq, eq); }
+    __syncthreads();
+    if (threadIdx.x == 0) { block_gt[blockIdx.x] = s_gt; block_eq[blockIdx.x] = s_eq; }
+}
+
+// one block: exclusive scans of the per-block counts, in place
+__global__ void __launch_bounds__(1024) topk_scan(uint32_t* block_gt, uint32_t* block_eq, uint32_t nb)
+{
+    __shared__ uint32_t wsum[2][32];
+    __shared__ uint32_t carry[2];
+    const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
+    if (t == 0) { carry[0] = 0u; carry[1] = 0u; }
+    __syncthreads();
+    for (uint32_t base = 0; base < nb; base += 1024u) {
+        const uint32_t i = base + t;
+        uint32_t v[2] = { i < nb ? block_gt[i] : 0u, i < nb ? block_eq[i] : 0u };
+        uint32_t inc[2] = { v[0], v[1] };
+        for (int q = 0; q < 2; ++q) {
+            for (int off = 1; off < 32; off <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc[q], off);
+                if ((int)lane >= off) inc[q] += o;
+            }
+            if (lane == 31u) wsum[q][warp] = inc[q];
+        }
+        __syncthreads();
+        if (warp == 0) {
+            for (int q = 0; q < 2; ++q) {
+                uint32_t w = wsum[q][lane], wi = w;
+                for (int off = 1; off < 32; off <<= 1) {
+                    const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, wi, off);
+                    if ((int)lane >= off) wi += o;
+                }
+                wsum[q][lane] = wi - w;  // exclusive
+            }
+        }
+        __syncthreads();
+        uint32_t tot[2];
+        for (int q = 0; q < 2; ++q) {
+            const uint32_t excl = carry[q] + wsum[q][warp] + inc[q] - v[q];
+            if (i < nb) (q == 0 ? block_gt : block_eq)[i] = excl;
+            tot[q] = excl + v[q];
+        }
+        __syncthreads();
+        if (t == 1023u) { carry[0] = tot[0]; carry[1] = tot[1]; }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) topk_emit(const float* __restrict__ score, uint32_t n, int worst, const TopkState* st,
+                                                 const uint32_t* block_gt, const uint32_t* block_eq, uint32_t* out_idx)
+{
+    __shared__ uint32_t w_gt[8], w_eq[8];
+    __shared__ uint32_t run_gt, run_eq;
+    const uint32_t T = st->threshold, need = st->need_eq, total_eq = st->total_eq;
+    // "best": the first `need` equal keys by index; "worst": the last `need`
+    const uint32_t eq_lo = worst ? total_eq - need : 0u, eq_hi = worst ? total_eq : need;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { run_gt = block_gt[blockIdx.x]; run_eq = block_eq[blockIdx.x]; }
+    __syncthreads();
+    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
+    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+        bool gt = false, eq = false;
+        if (i < n) {
+            const uint32_t key = select_key(__ldg(score + i), worst);
+            gt = key > T;
+            eq = key == T;
+        }
+        const uint32_t bg = __ballot_sync(0xFFFFFFFFu, gt), be = __ballot_sync(0xFFFFFFFFu, eq);
+        const uint32_t lt_mask = (1u << lane) - 1u;
+        if (lane == 0) { w_gt[warp] = __popc(bg); w_eq[warp] = __popc(be); }
+        __syncthreads();
+        uint32_t gt_before = run_gt + __popc(bg & lt_mask), eq_before = run_eq + __popc(be & lt_mask);
+        for (uint32_t w = 0; w < warp; ++w) { gt_before += w_gt[w]; eq_before += w_eq[w]; }
+        // position among the selected = selected elements with a lower index
+        const uint32_t eq_sel_before = eq_before <= eq_lo ? 0u : (eq_before >= eq_hi ? eq_hi - eq_lo : eq_before - eq_lo);
+        if (gt) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
+        else if (eq && eq_before >= eq_lo && eq_before < eq_hi) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t g = 0u, e = 0u;
+            for (uint32_t w = 0; w < 8u; ++w) { g += w_gt[w]; e += w_eq[w]; }
+            run_gt += g; run_eq += e;
+        }
+        __syncthreads();
+    }
+}
+
+// ---- migration payloads ---------------------------------------------------------
+// box layout: k rows of `stride` words, then k scores
+__global__ void pack_rows(const uint32_t* __restrict__ rows, const float* __restrict__ score, const uint32_t* __restrict__ idx,
+                          uint32_t k, uint32_t stride, uint32_t* box)
+{
+    const uint32_t nblk = stride >> 2;
+    const uint64_t total = (uint64_t)k * nblk;
+    float* box_score = reinterpret_cast<float*>(box + (size_t)k * stride);
+    for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t j = (uint32_t)(e / nblk), b = (uint32_t)(e % nblk);
+        const uint32_t src = idx[j];
+        reinterpret_cast<uint4*>(box)[e] = __ldg(reinterpret_cast<const uint4*>(rows) + (size_t)src * nblk + b);
+        if (b == 0) box_score[j] = score[src];
+    }
+}
+
+__global__ void unpack_rows(uint32_t* rows, float* score, const uint32_t* __restrict__ idx, uint32_t k, uint32_t stride,
+                            const uint32_t* __restrict__ box)
+{
+    const uint32_t nblk = stride >> 2;
+    const uint64_t total = (uint64_t)k * nblk;
+    const float* box_score = reinterpret_cast<const float*>(box + (size_t)k * stride);
+    for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t j = (uint32_t)(e / nblk), b = (uint32_t)(e % nblk);
+        const uint32_t dst = idx[j];
+        reinterpret_cast<uint4*>(rows)[(size_t)dst * nblk + b] = __ldg(reinterpret_cast<const uint4*>(box) + e);
+        if (b == 0) score[dst] = box_score[j];
+    }
+}
+
+// host rows are unpadded; device rows are padded to a multiple of 4 words
+__global__ void repack_rows(const uint32_t* __restrict__ src, uint32_t* dst, uint64_t n, uint32_t src_stride, uint32_t dst_stride)
+{
+    const uint64_t total = n * dst_stride;
+    for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t i = e / dst_stride;
+        const uint32_t j = (uint32_t)(e % dst_stride);
+        dst[e] = j < src_stride ? src[i * src_stride + j] : 0u;
+    }
+}
+
+}  // namespace pgak

@@ -219,6 +219,7 @@ opga_t *opga_init(uint64_t seed) /* src/pga.cu:148-164 */
 	p->seed = seed;
 	p->threads = 1;
 	p->delay = 1;
+	p->topology = OPGA_TOPO_RANDOM; /* "random migrations", include/pga.h:148 */
 	return p;
 }
 
