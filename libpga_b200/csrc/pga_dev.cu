@@ -43,6 +43,10 @@ struct pgadev_ctx {
     unsigned long long launches;
     ncclComm_t comm;
     int hook_threads;  // $PGA_HOOK_THREADS override, 0 = automatic
+    // tuning knobs, settable from the environment for on-device experiments
+    uint32_t fast_blocks_per_sm;  // $PGA_FAST_BLOCKS_PER_SM: grid cap of the fast kernels
+    uint32_t l2_load, l2_store;   // $PGA_L2_LOAD / $PGA_L2_STORE: 0 normal, 1 evict_last, 2 evict_first
+    int force_generic;            // $PGA_FORCE_GENERIC=1: skip the compile-time tiled kernels
 };
 
 struct pgadev_pop {
@@ -103,6 +107,11 @@ extern "C" pgadev_ctx* pgadev_ctx_create(void)
     CCE(cudaEventCreate(&c->t1));
     const char* ht = getenv("PGA_HOOK_THREADS");
     c->hook_threads = ht ? atoi(ht) : 0;
+    const char* e;
+    c->fast_blocks_per_sm = (e = getenv("PGA_FAST_BLOCKS_PER_SM")) && atoi(e) > 0 ? (uint32_t)atoi(e) : 16u;
+    c->l2_load = (e = getenv("PGA_L2_LOAD")) ? (uint32_t)atoi(e) : 0u;
+    c->l2_store = (e = getenv("PGA_L2_STORE")) ? (uint32_t)atoi(e) : 0u;
+    c->force_generic = (e = getenv("PGA_FORCE_GENERIC")) ? atoi(e) : 0;
     const char* stack = getenv("PGA_STACK_BYTES");  // device stack for deep user hooks
     if (stack && atoi(stack) > 0) CCE(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(stack)));
     return c;
@@ -264,9 +273,49 @@ static int launch_fast_inst(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
     return 0;
 }
 
+template <int ENC, int OBJ, int LOGG, int NB>
+static int launch_tiled_inst(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+{
+    constexpr int G = 1 << LOGG;
+    constexpr int TB = NB >= 2 ? 2 : (G < 4 ? G : 4);  // 2*TB*NB parent loads in flight per lane
+    const uint32_t grid = grid_for(p->n, 256, (uint32_t)c->sm_count * c->fast_blocks_per_sm);
+    generation_fused_tiled<ENC, OBJ, LOGG, NB, TB><<<grid, 256, 0, c->stream>>>(a);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+// shapes with a compile-time tiling: up to 32 blocks per row with any group size,
+// up to 128 blocks per row with full-warp groups; anything else takes the generic kernel
+template <int ENC, int OBJ>
+static int launch_tiled(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+{
+    const uint32_t nblk = p->stride >> 2, G = p->group, NBr = (nblk + G - 1) / G;
+    if (c->force_generic) return 1;
+    if (NBr == 1) {
+        switch (G) {
+            case 1: return launch_tiled_inst<ENC, OBJ, 0, 1>(c, p, a);
+            case 2: return launch_tiled_inst<ENC, OBJ, 1, 1>(c, p, a);
+            case 4: return launch_tiled_inst<ENC, OBJ, 2, 1>(c, p, a);
+            case 8: return launch_tiled_inst<ENC, OBJ, 3, 1>(c, p, a);
+            case 16: return launch_tiled_inst<ENC, OBJ, 4, 1>(c, p, a);
+            default: return launch_tiled_inst<ENC, OBJ, 5, 1>(c, p, a);
+        }
+    }
+    if (G == 32) {
+        if (NBr == 2) return launch_tiled_inst<ENC, OBJ, 5, 2>(c, p, a);
+        if (NBr == 3) return launch_tiled_inst<ENC, OBJ, 5, 3>(c, p, a);
+        if (NBr == 4) return launch_tiled_inst<ENC, OBJ, 5, 4>(c, p, a);
+    }
+    return 1;
+}
+
 template <int ENC, int OBJ>
 static int launch_fast_ph(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a, uint32_t ph)
 {
+    if (ph == PH_FUSED) {
+        const int rc = launch_tiled<ENC, OBJ>(c, p, a);
+        if (rc <= 0) return rc;
+    }
     switch (ph) {
         case PH_FUSED: return launch_fast_inst<ENC, PH_FUSED, OBJ>(c, p, a);
         case PH_EVALUATE: return launch_fast_inst<ENC, PH_EVALUATE, OBJ>(c, p, a);
@@ -297,6 +346,8 @@ extern "C" int pgadev_launch(pgadev_ctx* c, pgadev_pop* p, const pgadev_step* st
     a.lenf = (float)p->len;
     a.stride = p->stride;
     a.group = p->group;
+    a.l2_load = c->l2_load;
+    a.l2_store = c->l2_store;
     a.draw = make_draw(st->seed, st->island, st->epoch);
     a.objective = st->objective;
     a.obj = (obj_fn)st->obj_hook;

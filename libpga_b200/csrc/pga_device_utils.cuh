@@ -18,11 +18,12 @@ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
 {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
-        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-        const uint32_t n0 = hi1 ^ c1 ^ k0;
-        const uint32_t n2 = hi0 ^ c3 ^ k1;
-        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        // one IMAD.WIDE.U32 per product: high and low halves together
+        const unsigned long long m0 = (unsigned long long)0xD2511F53u * c0;
+        const unsigned long long m1 = (unsigned long long)0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t)(m1 >> 32) ^ c1 ^ k0;
+        const uint32_t n2 = (uint32_t)(m0 >> 32) ^ c3 ^ k1;
+        c0 = n0; c1 = (uint32_t)m1; c2 = n2; c3 = (uint32_t)m0;
         k0 += 0x9E3779B9u;
         k1 += 0xBB67AE85u;
     }
@@ -55,6 +56,43 @@ __device__ __forceinline__ uint32_t draw_index(float u, float nf, uint32_t n)
 {
     const uint32_t v = __float2uint_rz(__fmul_rn(u, nf));
     return v < n ? v : n - 1u;
+}
+
+// rand > 0.5 (src/pga.cu:137) on the raw word: (x >> 8) * 2^-24 > 0.5  <=>  x >= 0x80000100
+__device__ __forceinline__ bool draw_above_half(uint32_t x)
+{
+    return x > 0x800000FFu;
+}
+
+// ---- L2 eviction hints on the population rows -------------------------------
+// Parent rows are gathered at random and re-read ~2x per generation; child rows
+// are written once and not read before the next launch.  The policy pair is a
+// launch parameter so it can be tuned on the device without rebuilding.
+enum : uint32_t { L2_NORMAL = 0u, L2_EVICT_LAST = 1u, L2_EVICT_FIRST = 2u };
+
+__device__ __forceinline__ uint64_t l2_policy(uint32_t which)
+{
+    uint64_t p;
+    if (which == L2_EVICT_LAST) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    else if (which == L2_EVICT_FIRST) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+
+__device__ __forceinline__ uint4 load_row_block(const uint4* p, uint64_t policy)
+{
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p), "l"(policy));
+    return v;
+}
+
+__device__ __forceinline__ void store_row_block(uint4* p, const uint4& v, uint64_t policy)
+{
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w),
+                 "l"(policy)
+                 : "memory");
 }
 
 // ---- ranking key: higher score first, then lower index; NaN below everything ----

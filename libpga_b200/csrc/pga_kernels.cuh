@@ -44,6 +44,7 @@ struct GenArgs {
     float lenf;      // (float)len
     uint32_t stride; // 32-bit words per stored row, multiple of 4
     uint32_t group;  // fast path: lanes per child (power of two <= 32)
+    uint32_t l2_load, l2_store;  // L2 eviction hints for parent loads / child stores
     DrawCtx draw;
     int objective;
     obj_fn obj;
@@ -362,6 +363,154 @@ __global__ void __launch_bounds__(256) generation_fast(const __grid_constant__ G
         }
     }
     if (PH & PH_EVALUATE) block_best_commit(key, a.best + a.best_slot, warp_best);
+}
+
+// ---- fused generation, tiled -----------------------------------------------------
+//
+// The same algorithm as generation_fast<.., PH_FUSED, ..> with the shape known at
+// compile time: G = 2^LOGG lanes per child, NB 16-byte blocks per lane, TB tiles
+// batched so that 2*TB*NB independent 128-bit parent loads are in flight per lane
+// before any of them is consumed.  This is the kernel the roofline numbers are
+// quoted on.
+template <int ENC, int OBJ, int LOGG, int NB, int TB>
+__global__ void __launch_bounds__(256) generation_fused_tiled(const __grid_constant__ GenArgs a)
+{
+    constexpr uint32_t G = 1u << LOGG, CPT = 32u / G;
+    __shared__ unsigned long long warp_best[8];
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t nblk = a.stride >> 2;
+    const uint32_t gl = lane & (G - 1u), grp = lane >> LOGG;
+    const uint4* __restrict__ cur = reinterpret_cast<const uint4*>(a.cur);
+    uint4* __restrict__ nxt = reinterpret_cast<uint4*>(a.nxt);
+    const uint64_t pol_ld = l2_policy(a.l2_load), pol_st = l2_policy(a.l2_store);
+
+    if (blockIdx.x == 0 && threadIdx.x == 0) a.best[(a.best_slot + 1u) & 3u] = 0ull;
+
+    unsigned long long key = 0ull;
+
+    for (uint64_t cbase64 = (uint64_t)gwarp * 32u; cbase64 < a.n; cbase64 += (uint64_t)nwarps * 32u) {
+        const uint32_t cbase = (uint32_t)cbase64;
+        const uint32_t mine = cbase + lane;
+        const bool have = mine < a.n;
+
+        // lane j: tournaments and mutation draw of child cbase + j
+        uint32_t p1 = 0, p2 = 0, m_idx = 0, m_val = 0;
+        bool m_on = false;
+        if (have) {
+            const uint4 w = draw_block(a.draw, STREAM_ROW, mine, 0);
+            const float u0 = to_uniform(w.x), u1 = to_uniform(w.y), u2 = to_uniform(w.z), u3 = to_uniform(w.w);
+            p1 = tournament(a.score_in, u0, u1, a.nf, a.n);
+            p2 = tournament(a.score_in, u2, u3, a.nf, a.n);
+            if (a.sel) { a.sel[2 * (size_t)mine] = (int32_t)p1; a.sel[2 * (size_t)mine + 1] = (int32_t)p2; }
+            m_on = u1 <= PGA_MUTATION_CHANCE;
+            m_idx = draw_index(u0, a.lenf, a.len);
+            m_val = ENC == ENC_BITS ? (u2 > 0.5f ? 1u : 0u) : __float_as_uint(u2);
+        }
+        const uint32_t any_mut = __ballot_sync(0xFFFFFFFFu, m_on);  // 72 % of warps: none
+
+        float my_score = 0.f;
+#pragma unroll 1
+        for (uint32_t tile0 = 0; tile0 < G; tile0 += TB) {
+            uint4 x[TB][NB], y[TB][NB];
+            // issue every parent load of the batch
+#pragma unroll
+            for (int tb = 0; tb < TB; ++tb) {
+                const uint32_t src_lane = (tile0 + tb) * CPT + grp;
+                const uint32_t q1 = __shfl_sync(0xFFFFFFFFu, p1, src_lane);
+                const uint32_t q2 = __shfl_sync(0xFFFFFFFFu, p2, src_lane);
+                const bool valid = cbase + src_lane < a.n;
+#pragma unroll
+                for (int nb = 0; nb < NB; ++nb) {
+                    const uint32_t b = gl + (uint32_t)nb * G;
+                    if (valid && b < nblk) {
+                        x[tb][nb] = load_row_block(cur + (size_t)q1 * nblk + b, pol_ld);
+                        y[tb][nb] = load_row_block(cur + (size_t)q2 * nblk + b, pol_ld);
+                    } else {
+                        x[tb][nb] = make_uint4(0u, 0u, 0u, 0u);
+                        y[tb][nb] = make_uint4(0u, 0u, 0u, 0u);
+                    }
+                }
+            }
+            // consume
+#pragma unroll
+            for (int tb = 0; tb < TB; ++tb) {
+                const uint32_t src_lane = (tile0 + tb) * CPT + grp;
+                const uint32_t child = cbase + src_lane;
+                const bool valid = child < a.n;
+                uint32_t c_idx = 0, c_val = 0;
+                if (any_mut) {  // warp-uniform
+                    c_idx = __shfl_sync(0xFFFFFFFFu, m_idx, src_lane);
+                    c_val = __shfl_sync(0xFFFFFFFFu, m_val, src_lane);
+                }
+                const bool c_on = (any_mut >> src_lane) & 1u;
+                const uint32_t c_blk = ENC == ENC_BITS ? (c_idx >> 7) : (c_idx >> 2);
+                float facc = 0.f;
+                uint32_t iacc = 0;
+#pragma unroll
+                for (int nb = 0; nb < NB; ++nb) {
+                    const uint32_t b = gl + (uint32_t)nb * G;
+                    if (valid && b < nblk) {
+                        const uint4 xx = x[tb][nb], yy = y[tb][nb];
+                        uint4 c;
+                        if (ENC == ENC_BITS) {
+                            const uint4 m = draw_block(a.draw, STREAM_MASK, child, b);
+                            c.x = (xx.x & m.x) | (yy.x & ~m.x);
+                            c.y = (xx.y & m.y) | (yy.y & ~m.y);
+                            c.z = (xx.z & m.z) | (yy.z & ~m.z);
+                            c.w = (xx.w & m.w) | (yy.w & ~m.w);
+                        } else {
+                            const uint4 w = draw_block(a.draw, STREAM_ROW, child, b);
+                            c.x = draw_above_half(w.x) ? xx.x : yy.x;  // src/pga.cu:137-141
+                            c.y = draw_above_half(w.y) ? xx.y : yy.y;
+                            c.z = draw_above_half(w.z) ? xx.z : yy.z;
+                            c.w = draw_above_half(w.w) ? xx.w : yy.w;
+                        }
+                        if (c_on && c_blk == b) {  // src/pga.cu:127-133; rare
+                            if (ENC == ENC_BITS) {
+                                const uint32_t word = (c_idx >> 5) & 3u, bit = 1u << (c_idx & 31u);
+                                uint32_t* cw = word == 0 ? &c.x : word == 1 ? &c.y : word == 2 ? &c.z : &c.w;
+                                *cw = c_val ? (*cw | bit) : (*cw & ~bit);
+                            } else {
+                                const uint32_t e = c_idx & 3u;
+                                if (e == 0) c.x = c_val; else if (e == 1) c.y = c_val; else if (e == 2) c.z = c_val; else c.w = c_val;
+                            }
+                        }
+                        if (ENC == ENC_BITS) {
+                            iacc += __popc(c.x) + __popc(c.y) + __popc(c.z) + __popc(c.w);
+                        } else {
+                            const uint32_t j = 4u * b;
+                            if (j + 0 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.x));
+                            if (j + 1 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.y));
+                            if (j + 2 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.z));
+                            if (j + 3 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.w));
+                        }
+                        store_row_block(nxt + (size_t)child * nblk + b, c, pol_st);
+                    }
+                }
+                float s;
+                if (ENC == ENC_BITS) {
+#pragma unroll
+                    for (uint32_t off = G >> 1; off >= 1u; off >>= 1) iacc += __shfl_xor_sync(0xFFFFFFFFu, iacc, off);
+                    s = __uint2float_rn(iacc);
+                } else {
+#pragma unroll
+                    for (uint32_t off = G >> 1; off >= 1u; off >>= 1)
+                        facc = __fadd_rn(facc, __shfl_xor_sync(0xFFFFFFFFu, facc, off));
+                    s = obj_finalize<OBJ>(facc, a.len);
+                }
+                const float v = __shfl_sync(0xFFFFFFFFu, s, (lane & (CPT - 1u)) << LOGG);
+                if ((lane >> (5 - LOGG)) == tile0 + (uint32_t)tb) my_score = v;
+            }
+        }
+        if (have) {
+            a.score_out[mine] = my_score;
+            const unsigned long long k = best_key(my_score, mine);
+            key = k > key ? k : key;
+        }
+    }
+    block_best_commit(key, a.best + a.best_slot, warp_best);
 }
 
 // ---- population set-up (src/pga.cu:81-86, :116-117): genes := rand row of epoch 0 ----

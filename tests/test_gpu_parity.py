@@ -168,6 +168,48 @@ def test_onemax_trajectory(pga, oracle, size, bits, gens):
     o.close()
 
 
+# every compile-time tiling of the fused kernel (lanes per child x blocks per lane), ragged sizes
+BIT_SHAPES = [33, 200, 400, 1000, 2000, 4096, 5000, 12000, 16000, 20000]
+F32_SHAPES = [4, 7, 16, 40, 100, 128, 256, 300, 500, 1000]
+
+
+@pytest.mark.parametrize("bits", BIT_SHAPES)
+@pytest.mark.parametrize("generic", [False, True])
+def test_onemax_shapes(pga, oracle, monkeypatch, bits, generic):
+    if generic:
+        monkeypatch.setenv("PGA_FORCE_GENERIC", "1")
+    g, o, gp, op = setup_pair(pga, oracle, 13, 211, bits, encoding=pg.GENES_BITS, builtin=pg.OBJ_ONEMAX)
+    gp.capture_selection(True)
+    g.run(4); o.run(4)
+    assert np.array_equal(gp.selection(), op.selection())
+    assert np.array_equal(gp.genes(), op.genes())
+    assert np.array_equal(gp.scores(), op.scores())
+    o.close()
+
+
+@pytest.mark.parametrize("length", F32_SHAPES)
+@pytest.mark.parametrize("generic", [False, True])
+def test_rastrigin_shapes(pga, oracle, monkeypatch, length, generic):
+    if generic:
+        monkeypatch.setenv("PGA_FORCE_GENERIC", "1")
+    g, o, gp, op = setup_pair(pga, oracle, 13, 211, length, builtin=pg.OBJ_RASTRIGIN)
+    g.run(4); o.run(4)
+    assert_scores_close(gp.scores(), op.scores())
+    assert same_bits(gp.genes(), op.genes())
+    assert same_bits(gp.scores(), op.scores())
+    o.close()
+
+
+@pytest.mark.parametrize("policy", [("1", "2"), ("2", "1"), ("1", "0")])
+def test_l2_hints_do_not_change_results(pga, oracle, monkeypatch, policy):
+    monkeypatch.setenv("PGA_L2_LOAD", policy[0])
+    monkeypatch.setenv("PGA_L2_STORE", policy[1])
+    g, o, gp, op = setup_pair(pga, oracle, 5, 5000, 1024, encoding=pg.GENES_BITS, builtin=pg.OBJ_ONEMAX)
+    g.run(5); o.run(5)
+    assert np.array_equal(gp.genes(), op.genes())
+    o.close()
+
+
 def test_onemax_full_size_lockstep(pga, oracle):
     # config 2 at full size: 2^20 x 1024 bits, three lock-step generations
     n, bits = 1 << 20, 1024
