@@ -45,8 +45,9 @@ struct pgadev_ctx {
     int hook_threads;  // $PGA_HOOK_THREADS override, 0 = automatic
     // tuning knobs, settable from the environment for on-device experiments
     uint32_t fast_blocks_per_sm;  // $PGA_FAST_BLOCKS_PER_SM: grid cap of the fast kernels
-    uint32_t l2_load, l2_store;   // $PGA_L2_LOAD / $PGA_L2_STORE: 0 normal, 1 evict_last, 2 evict_first
+    int fast_blocks_per_sm_set;
     int force_generic;            // $PGA_FORCE_GENERIC=1: skip the compile-time tiled kernels
+    int staged;                   // $PGA_STAGED=1: small rows take the cp.async-staged kernel instead
 };
 
 struct pgadev_pop {
@@ -109,9 +110,9 @@ extern "C" pgadev_ctx* pgadev_ctx_create(void)
     c->hook_threads = ht ? atoi(ht) : 0;
     const char* e;
     c->fast_blocks_per_sm = (e = getenv("PGA_FAST_BLOCKS_PER_SM")) && atoi(e) > 0 ? (uint32_t)atoi(e) : 16u;
-    c->l2_load = (e = getenv("PGA_L2_LOAD")) ? (uint32_t)atoi(e) : 0u;
-    c->l2_store = (e = getenv("PGA_L2_STORE")) ? (uint32_t)atoi(e) : 0u;
+    c->fast_blocks_per_sm_set = e && atoi(e) > 0;
     c->force_generic = (e = getenv("PGA_FORCE_GENERIC")) ? atoi(e) : 0;
+    c->staged = (e = getenv("PGA_STAGED")) ? atoi(e) : 0;
     const char* stack = getenv("PGA_STACK_BYTES");  // device stack for deep user hooks
     if (stack && atoi(stack) > 0) CCE(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(stack)));
     return c;
@@ -273,39 +274,119 @@ static int launch_fast_inst(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
     return 0;
 }
 
-template <int ENC, int OBJ, int LOGG, int NB>
-static int launch_tiled_inst(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+// Tile batch and occupancy target per shape, from the B200 sweeps in
+// profiles/r1_sweeps.md: packed bits run best with 16 parent loads in flight per
+// lane at 2 blocks/SM, f32 rows (more ALU work per byte) with 8 at 3 blocks/SM.
+template <int ENC, int LOGG, int NB>
+struct TiledShape {
+    static constexpr int G = 1 << LOGG;
+    static constexpr int TB = ENC == ENC_BITS ? (NB <= 2 ? (G < 4 ? G : 4) : 2) : (NB >= 2 ? 2 : (G < 4 ? G : 4));
+    static constexpr int MINB = ENC == ENC_BITS ? 2 : 3;
+};
+
+template <int ENC, int OBJ, int LOGG, int NB, bool EXACT>
+static int launch_tiled_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
-    constexpr int G = 1 << LOGG;
-    constexpr int TB = NB >= 2 ? 2 : (G < 4 ? G : 4);  // 2*TB*NB parent loads in flight per lane
-    const uint32_t grid = grid_for(p->n, 256, (uint32_t)c->sm_count * c->fast_blocks_per_sm);
-    generation_fused_tiled<ENC, OBJ, LOGG, NB, TB><<<grid, 256, 0, c->stream>>>(a);
+    constexpr int TB = TiledShape<ENC, LOGG, NB>::TB, MINB = TiledShape<ENC, LOGG, NB>::MINB;
+    static int configured_for = -1;
+    static int blocks_per_sm = 2;
+    if (configured_for != c->device) {
+        CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, generation_fused_tiled<ENC, OBJ, LOGG, NB, TB, EXACT, MINB>, 256, 0));
+        if (blocks_per_sm < 1) blocks_per_sm = 1;
+        configured_for = c->device;
+    }
+    // exactly one resident wave (a partial second wave costs a full kernel tail)
+    const uint32_t per_sm = c->fast_blocks_per_sm_set ? c->fast_blocks_per_sm : (uint32_t)blocks_per_sm;
+    const uint32_t grid = grid_for(p->n, 256, (uint32_t)c->sm_count * per_sm);
+    generation_fused_tiled<ENC, OBJ, LOGG, NB, TB, EXACT, MINB><<<grid, 256, 0, c->stream>>>(a);
     LAUNCH_CHECK(c);
     return 0;
 }
 
-// shapes with a compile-time tiling: up to 32 blocks per row with any group size,
-// up to 128 blocks per row with full-warp groups; anything else takes the generic kernel
+template <int ENC, int OBJ, int LOGG, int NB>
+static int launch_tiled_inst(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+{
+    // EXACT: every lane of a group owns exactly NB blocks and (f32) no gene is padding
+    const bool exact = (p->stride >> 2) == (uint32_t)NB << LOGG && (ENC == ENC_BITS || p->len == p->stride);
+    return exact ? launch_tiled_one<ENC, OBJ, LOGG, NB, true>(c, p, a) : launch_tiled_one<ENC, OBJ, LOGG, NB, false>(c, p, a);
+}
+
+// small rows (<= 128 B): per-warp cp.async pipeline through shared memory.  Slower
+// than the register-tiled kernel on B200 (95 vs 73 us per OneMax generation), kept
+// selectable with $PGA_STAGED=1 as the measured alternative.
+template <int ENC, int OBJ, int LOGG, bool EXACT, int WARPS>
+static int launch_staged_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+{
+    constexpr size_t smem = (size_t)WARPS * 2u * 64u * (16u << LOGG);
+    static int configured_for = -1;
+    static int blocks_per_sm = 1;
+    if (configured_for != c->device) {
+        CCE(cudaFuncSetAttribute(generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem));
+        CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS>,
+                                                          WARPS * 32, smem));
+        if (blocks_per_sm < 1) blocks_per_sm = 1;
+        configured_for = c->device;
+    }
+    const uint32_t grid = grid_for(p->n, WARPS * 32u, (uint32_t)(c->sm_count * blocks_per_sm));
+    generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS><<<grid, WARPS * 32, smem, c->stream>>>(a);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+template <int ENC, int OBJ>
+static int launch_staged(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+{
+    const uint32_t nblk = p->stride >> 2, G = p->group;
+    if (!c->staged || c->force_generic || nblk > G || G > 8) return 1;
+    const bool exact = nblk == G && (ENC == ENC_BITS || p->len == p->stride);
+#define ST(L) return exact ? launch_staged_one<ENC, OBJ, L, true, 4>(c, p, a) : launch_staged_one<ENC, OBJ, L, false, 4>(c, p, a)
+    switch (G) {
+        case 1: ST(0);
+        case 2: ST(1);
+        case 4: ST(2);
+        default: ST(3);
+    }
+#undef ST
+}
+
+// Shapes with a compile-time tiling.  f32 rows keep the oracle's canonical group
+// (G = min(32, pow2ceil(blocks)) lanes, NB = blocks per lane up to 4).  Packed bits
+// have an order-free integer score, so they use half as many lanes with two blocks
+// each (fewer shuffles and reductions per child).  Anything larger takes the
+// generic kernel.
 template <int ENC, int OBJ>
 static int launch_tiled(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
-    const uint32_t nblk = p->stride >> 2, G = p->group, NBr = (nblk + G - 1) / G;
+    const uint32_t nblk = p->stride >> 2;
     if (c->force_generic) return 1;
+    uint32_t G = p->group;
+    if (ENC == ENC_BITS && nblk >= 2 && nblk <= 32) G = p->group / 2;  // pow2ceil(nblk) / 2 lanes, two blocks each
+    const uint32_t NBr = (nblk + G - 1) / G;
+#define TL(L, N) return launch_tiled_inst<ENC, OBJ, L, N>(c, p, a)
     if (NBr == 1) {
         switch (G) {
-            case 1: return launch_tiled_inst<ENC, OBJ, 0, 1>(c, p, a);
-            case 2: return launch_tiled_inst<ENC, OBJ, 1, 1>(c, p, a);
-            case 4: return launch_tiled_inst<ENC, OBJ, 2, 1>(c, p, a);
-            case 8: return launch_tiled_inst<ENC, OBJ, 3, 1>(c, p, a);
-            case 16: return launch_tiled_inst<ENC, OBJ, 4, 1>(c, p, a);
-            default: return launch_tiled_inst<ENC, OBJ, 5, 1>(c, p, a);
+            case 1: TL(0, 1);
+            case 2: TL(1, 1);
+            case 4: TL(2, 1);
+            case 8: TL(3, 1);
+            case 16: TL(4, 1);
+            default: TL(5, 1);
         }
     }
-    if (G == 32) {
-        if (NBr == 2) return launch_tiled_inst<ENC, OBJ, 5, 2>(c, p, a);
-        if (NBr == 3) return launch_tiled_inst<ENC, OBJ, 5, 3>(c, p, a);
-        if (NBr == 4) return launch_tiled_inst<ENC, OBJ, 5, 4>(c, p, a);
+    if (NBr == 2) {
+        switch (G) {
+            case 1: TL(0, 2);
+            case 2: TL(1, 2);
+            case 4: TL(2, 2);
+            case 8: TL(3, 2);
+            case 16: TL(4, 2);
+            default: TL(5, 2);
+        }
     }
+    if (G == 32 && NBr == 3) TL(5, 3);
+    if (G == 32 && NBr == 4) TL(5, 4);
+#undef TL
     return 1;
 }
 
@@ -313,7 +394,9 @@ template <int ENC, int OBJ>
 static int launch_fast_ph(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a, uint32_t ph)
 {
     if (ph == PH_FUSED) {
-        const int rc = launch_tiled<ENC, OBJ>(c, p, a);
+        int rc = launch_staged<ENC, OBJ>(c, p, a);
+        if (rc <= 0) return rc;
+        rc = launch_tiled<ENC, OBJ>(c, p, a);
         if (rc <= 0) return rc;
     }
     switch (ph) {
@@ -346,8 +429,6 @@ extern "C" int pgadev_launch(pgadev_ctx* c, pgadev_pop* p, const pgadev_step* st
     a.lenf = (float)p->len;
     a.stride = p->stride;
     a.group = p->group;
-    a.l2_load = c->l2_load;
-    a.l2_store = c->l2_store;
     a.draw = make_draw(st->seed, st->island, st->epoch);
     a.objective = st->objective;
     a.obj = (obj_fn)st->obj_hook;

@@ -64,35 +64,21 @@ __device__ __forceinline__ bool draw_above_half(uint32_t x)
     return x > 0x800000FFu;
 }
 
-// ---- L2 eviction hints on the population rows -------------------------------
-// Parent rows are gathered at random and re-read ~2x per generation; child rows
-// are written once and not read before the next launch.  The policy pair is a
-// launch parameter so it can be tuned on the device without rebuilding.
-enum : uint32_t { L2_NORMAL = 0u, L2_EVICT_LAST = 1u, L2_EVICT_FIRST = 2u };
-
-__device__ __forceinline__ uint64_t l2_policy(uint32_t which)
-{
-    uint64_t p;
-    if (which == L2_EVICT_LAST) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
-    else if (which == L2_EVICT_FIRST) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-    else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
-    return p;
-}
-
-__device__ __forceinline__ uint4 load_row_block(const uint4* p, uint64_t policy)
+// ---- population row accesses ---------------------------------------------------
+// Parent rows: read-only path, no L1 allocation (a row is used once per child).
+// L2 eviction-priority hints (createpolicy evict_last on the gathers, evict_first
+// on the child stores, and the other combinations) were measured on B200 and made
+// no difference to time or DRAM traffic (profiles/r1_sweeps.md), so none are used.
+__device__ __forceinline__ uint4 load_row_block(const uint4* p)
 {
     uint4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
-                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                 : "l"(p), "l"(policy));
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
     return v;
 }
 
-__device__ __forceinline__ void store_row_block(uint4* p, const uint4& v, uint64_t policy)
+__device__ __forceinline__ void store_row_block(uint4* p, const uint4& v)
 {
-    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w),
-                 "l"(policy)
-                 : "memory");
+    asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
 // ---- ranking key: higher score first, then lower index; NaN below everything ----

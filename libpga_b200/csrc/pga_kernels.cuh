@@ -44,7 +44,6 @@ struct GenArgs {
     float lenf;      // (float)len
     uint32_t stride; // 32-bit words per stored row, multiple of 4
     uint32_t group;  // fast path: lanes per child (power of two <= 32)
-    uint32_t l2_load, l2_store;  // L2 eviction hints for parent loads / child stores
     DrawCtx draw;
     int objective;
     obj_fn obj;
@@ -370,21 +369,23 @@ __global__ void __launch_bounds__(256) generation_fast(const __grid_constant__ G
 // The same algorithm as generation_fast<.., PH_FUSED, ..> with the shape known at
 // compile time: G = 2^LOGG lanes per child, NB 16-byte blocks per lane, TB tiles
 // batched so that 2*TB*NB independent 128-bit parent loads are in flight per lane
-// before any of them is consumed.  This is the kernel the roofline numbers are
-// quoted on.
-template <int ENC, int OBJ, int LOGG, int NB, int TB>
-__global__ void __launch_bounds__(256) generation_fused_tiled(const __grid_constant__ GenArgs a)
+// before any of them is consumed.  EXACT says every lane owns exactly NB blocks
+// (row blocks == NB*G), which removes the per-block bounds test.  Children past
+// the end of the population are computed from row 0 and only their stores are
+// suppressed, so the loop body has no divergent region around the shuffles.
+// This is the kernel the roofline numbers are quoted on.
+template <int ENC, int OBJ, int LOGG, int NB, int TB, bool EXACT, int MINB>
+__global__ void __launch_bounds__(256, MINB) generation_fused_tiled(const __grid_constant__ GenArgs a)
 {
     constexpr uint32_t G = 1u << LOGG, CPT = 32u / G;
     __shared__ unsigned long long warp_best[8];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t nblk = a.stride >> 2;
+    const uint32_t nblk = EXACT ? (uint32_t)NB * G : a.stride >> 2;
     const uint32_t gl = lane & (G - 1u), grp = lane >> LOGG;
     const uint4* __restrict__ cur = reinterpret_cast<const uint4*>(a.cur);
     uint4* __restrict__ nxt = reinterpret_cast<uint4*>(a.nxt);
-    const uint64_t pol_ld = l2_policy(a.l2_load), pol_st = l2_policy(a.l2_store);
 
     if (blockIdx.x == 0 && threadIdx.x == 0) a.best[(a.best_slot + 1u) & 3u] = 0ull;
 
@@ -420,16 +421,13 @@ __global__ void __launch_bounds__(256) generation_fused_tiled(const __grid_const
                 const uint32_t src_lane = (tile0 + tb) * CPT + grp;
                 const uint32_t q1 = __shfl_sync(0xFFFFFFFFu, p1, src_lane);
                 const uint32_t q2 = __shfl_sync(0xFFFFFFFFu, p2, src_lane);
-                const bool valid = cbase + src_lane < a.n;
+                const uint4* r1 = cur + (size_t)q1 * nblk + gl;
+                const uint4* r2 = cur + (size_t)q2 * nblk + gl;
 #pragma unroll
                 for (int nb = 0; nb < NB; ++nb) {
-                    const uint32_t b = gl + (uint32_t)nb * G;
-                    if (valid && b < nblk) {
-                        x[tb][nb] = load_row_block(cur + (size_t)q1 * nblk + b, pol_ld);
-                        y[tb][nb] = load_row_block(cur + (size_t)q2 * nblk + b, pol_ld);
-                    } else {
-                        x[tb][nb] = make_uint4(0u, 0u, 0u, 0u);
-                        y[tb][nb] = make_uint4(0u, 0u, 0u, 0u);
+                    if (EXACT || gl + (uint32_t)nb * G < nblk) {
+                        x[tb][nb] = load_row_block(r1 + nb * G);
+                        y[tb][nb] = load_row_block(r2 + nb * G);
                     }
                 }
             }
@@ -446,12 +444,13 @@ __global__ void __launch_bounds__(256) generation_fused_tiled(const __grid_const
                 }
                 const bool c_on = (any_mut >> src_lane) & 1u;
                 const uint32_t c_blk = ENC == ENC_BITS ? (c_idx >> 7) : (c_idx >> 2);
+                uint4* out = nxt + (size_t)child * nblk + gl;
                 float facc = 0.f;
                 uint32_t iacc = 0;
 #pragma unroll
                 for (int nb = 0; nb < NB; ++nb) {
                     const uint32_t b = gl + (uint32_t)nb * G;
-                    if (valid && b < nblk) {
+                    if (EXACT || b < nblk) {
                         const uint4 xx = x[tb][nb], yy = y[tb][nb];
                         uint4 c;
                         if (ENC == ENC_BITS) {
@@ -481,12 +480,12 @@ __global__ void __launch_bounds__(256) generation_fused_tiled(const __grid_const
                             iacc += __popc(c.x) + __popc(c.y) + __popc(c.z) + __popc(c.w);
                         } else {
                             const uint32_t j = 4u * b;
-                            if (j + 0 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.x));
-                            if (j + 1 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.y));
-                            if (j + 2 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.z));
-                            if (j + 3 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.w));
+                            if (EXACT || j + 0 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.x));
+                            if (EXACT || j + 1 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.y));
+                            if (EXACT || j + 2 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.z));
+                            if (EXACT || j + 3 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.w));
                         }
-                        store_row_block(nxt + (size_t)child * nblk + b, c, pol_st);
+                        if (valid) store_row_block(out + nb * G, c);
                     }
                 }
                 float s;
@@ -509,6 +508,197 @@ __global__ void __launch_bounds__(256) generation_fused_tiled(const __grid_const
             const unsigned long long k = best_key(my_score, mine);
             key = k > key ? k : key;
         }
+    }
+    block_best_commit(key, a.best + a.best_slot, warp_best);
+}
+
+// ---- fused generation, staged (small rows) -------------------------------------
+//
+// For rows of at most 128 bytes (OneMax-1024, short float genomes) the register
+// version above is limited by how many parent loads a warp can keep in flight.
+// Here every warp runs its own three-deep software pipeline over its iterations
+// (32 children each):
+//     iteration i+2 : Philox block 0 + the four score gathers are issued
+//     iteration i+1 : tournaments resolved, both parent rows of all 32 children
+//                     copied global -> shared with 16-byte cp.async (LDGSTS),
+//                     8 KB in flight per warp, no registers held
+//     iteration i   : rows read back from shared memory, crossover mask drawn,
+//                     child mutated, scored, stored
+// Measured on B200 (scripts/microbench_stage.cu): for 128-byte rows one TMA bulk
+// copy per row is request-rate bound (68 us per 2^20-row pass) while cp.async
+// reaches the same 55 us as plain 128-bit loads, so the small-row path uses
+// cp.async and TMA bulk copies stay on the hook path, where rows are larger.
+struct SelDraw {
+    uint32_t c0, c1, c2, c3;  // tournament candidates
+    float s0, s1, s2, s3;     // their scores (loads in flight until sel_finish)
+    uint32_t m_idx, m_val;    // mutation target and value
+    bool m_on;
+};
+
+template <int ENC>
+__device__ __forceinline__ SelDraw sel_begin(const GenArgs& a, uint32_t child)
+{
+    SelDraw d;
+    const bool have = child < a.n;
+    const uint4 w = draw_block(a.draw, STREAM_ROW, child, 0);
+    const float u0 = to_uniform(w.x), u1 = to_uniform(w.y), u2 = to_uniform(w.z), u3 = to_uniform(w.w);
+    d.c0 = have ? draw_index(u0, a.nf, a.n) : 0u;
+    d.c1 = have ? draw_index(u1, a.nf, a.n) : 0u;
+    d.c2 = have ? draw_index(u2, a.nf, a.n) : 0u;
+    d.c3 = have ? draw_index(u3, a.nf, a.n) : 0u;
+    d.s0 = __ldg(a.score_in + d.c0);
+    d.s1 = __ldg(a.score_in + d.c1);
+    d.s2 = __ldg(a.score_in + d.c2);
+    d.s3 = __ldg(a.score_in + d.c3);
+    d.m_on = have && u1 <= PGA_MUTATION_CHANCE;
+    d.m_idx = draw_index(u0, a.lenf, a.len);
+    d.m_val = ENC == ENC_BITS ? (u2 > 0.5f ? 1u : 0u) : __float_as_uint(u2);
+    return d;
+}
+
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
+}
+
+template <int ENC, int OBJ, int LOGG, bool EXACT, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) generation_fused_staged(const __grid_constant__ GenArgs a)
+{
+    constexpr uint32_t G = 1u << LOGG, CPT = 32u / G, ROW = G * 16u, STAGE = 64u * ROW;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ unsigned long long warp_best[WARPS];
+    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    const uint32_t gl = lane & (G - 1u), grp = lane >> LOGG;
+    const uint32_t nblk = EXACT ? G : a.stride >> 2;
+    const bool in_row = EXACT || gl < nblk;
+    unsigned char* const my = smem_raw + (size_t)w * 2u * STAGE;
+    const uint4* __restrict__ cur = reinterpret_cast<const uint4*>(a.cur);
+    uint4* __restrict__ nxt = reinterpret_cast<uint4*>(a.nxt);
+
+    if (blockIdx.x == 0 && threadIdx.x == 0) a.best[(a.best_slot + 1u) & 3u] = 0ull;
+
+    const uint32_t gwarp = blockIdx.x * WARPS + w, nwarps = gridDim.x * WARPS;
+    const uint32_t total = (a.n + 31u) >> 5;  // warp iterations in the population
+    const uint32_t iters = gwarp < total ? (total - gwarp + nwarps - 1u) / nwarps : 0u;
+    unsigned long long key = 0ull;
+
+    // resolve the tournaments of iteration `it` and start its 64 row copies
+    auto issue = [&](const SelDraw& d, uint32_t it) {
+        const uint32_t mine = (gwarp + it * nwarps) * 32u + lane;
+        const uint32_t p1 = d.s0 < d.s1 ? d.c1 : d.c0;  // src/pga.cu:286-290
+        const uint32_t p2 = d.s2 < d.s3 ? d.c3 : d.c2;
+        if (a.sel && mine < a.n) { a.sel[2 * (size_t)mine] = (int32_t)p1; a.sel[2 * (size_t)mine + 1] = (int32_t)p2; }
+        unsigned char* st = my + (it & 1u) * STAGE;
+#pragma unroll
+        for (uint32_t tile = 0; tile < G; ++tile) {
+            const uint32_t c = tile * CPT + grp;
+            const uint32_t q1 = __shfl_sync(0xFFFFFFFFu, p1, c);
+            const uint32_t q2 = __shfl_sync(0xFFFFFFFFu, p2, c);
+            if (in_row) {
+                cp_async_16(st + (c * 2u + 0u) * ROW + gl * 16u, cur + (size_t)q1 * nblk + gl);
+                cp_async_16(st + (c * 2u + 1u) * ROW + gl * 16u, cur + (size_t)q2 * nblk + gl);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    SelDraw d1, d2;  // iteration i+1 (scores resolved at issue), iteration i+2 (gathers in flight)
+    uint32_t mut_idx0 = 0, mut_val0 = 0, any0 = 0;  // mutation data of the iteration being consumed
+    uint32_t mut_idx1 = 0, mut_val1 = 0, any1 = 0;
+    if (iters > 0) {
+        d1 = sel_begin<ENC>(a, gwarp * 32u + lane);
+        issue(d1, 0);
+        mut_idx1 = d1.m_idx; mut_val1 = d1.m_val; any1 = __ballot_sync(0xFFFFFFFFu, d1.m_on);
+    }
+    if (iters > 1) d2 = sel_begin<ENC>(a, (gwarp + nwarps) * 32u + lane);
+
+    for (uint32_t it = 0; it < iters; ++it) {
+        mut_idx0 = mut_idx1; mut_val0 = mut_val1; any0 = any1;
+        if (it + 1u < iters) {
+            issue(d2, it + 1u);
+            mut_idx1 = d2.m_idx; mut_val1 = d2.m_val; any1 = __ballot_sync(0xFFFFFFFFu, d2.m_on);
+            if (it + 2u < iters) d2 = sel_begin<ENC>(a, (gwarp + (it + 2u) * nwarps) * 32u + lane);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncwarp();
+
+        const uint32_t cbase = (gwarp + it * nwarps) * 32u;
+        const unsigned char* st = my + (it & 1u) * STAGE;
+        float my_score = 0.f;
+#pragma unroll
+        for (uint32_t tile = 0; tile < G; ++tile) {
+            const uint32_t c = tile * CPT + grp;
+            const uint32_t child = cbase + c;
+            uint32_t c_idx = 0, c_val = 0;
+            if (any0) {  // warp-uniform; 72 % of iterations have no mutation at all
+                c_idx = __shfl_sync(0xFFFFFFFFu, mut_idx0, c);
+                c_val = __shfl_sync(0xFFFFFFFFu, mut_val0, c);
+            }
+            const bool c_on = (any0 >> c) & 1u;
+            const uint32_t c_blk = ENC == ENC_BITS ? (c_idx >> 7) : (c_idx >> 2);
+            float facc = 0.f;
+            uint32_t iacc = 0;
+            if (in_row) {
+                const uint4 xx = *reinterpret_cast<const uint4*>(st + (c * 2u + 0u) * ROW + gl * 16u);
+                const uint4 yy = *reinterpret_cast<const uint4*>(st + (c * 2u + 1u) * ROW + gl * 16u);
+                uint4 o;
+                if (ENC == ENC_BITS) {
+                    const uint4 m = draw_block(a.draw, STREAM_MASK, child, gl);
+                    o.x = (xx.x & m.x) | (yy.x & ~m.x);
+                    o.y = (xx.y & m.y) | (yy.y & ~m.y);
+                    o.z = (xx.z & m.z) | (yy.z & ~m.z);
+                    o.w = (xx.w & m.w) | (yy.w & ~m.w);
+                } else {
+                    const uint4 r = draw_block(a.draw, STREAM_ROW, child, gl);
+                    o.x = draw_above_half(r.x) ? xx.x : yy.x;  // src/pga.cu:137-141
+                    o.y = draw_above_half(r.y) ? xx.y : yy.y;
+                    o.z = draw_above_half(r.z) ? xx.z : yy.z;
+                    o.w = draw_above_half(r.w) ? xx.w : yy.w;
+                }
+                if (c_on && c_blk == gl) {  // src/pga.cu:127-133; rare
+                    if (ENC == ENC_BITS) {
+                        const uint32_t word = (c_idx >> 5) & 3u, bit = 1u << (c_idx & 31u);
+                        uint32_t* cw = word == 0 ? &o.x : word == 1 ? &o.y : word == 2 ? &o.z : &o.w;
+                        *cw = c_val ? (*cw | bit) : (*cw & ~bit);
+                    } else {
+                        const uint32_t e = c_idx & 3u;
+                        if (e == 0) o.x = c_val; else if (e == 1) o.y = c_val; else if (e == 2) o.z = c_val; else o.w = c_val;
+                    }
+                }
+                if (ENC == ENC_BITS) {
+                    iacc = __popc(o.x) + __popc(o.y) + __popc(o.z) + __popc(o.w);
+                } else {
+                    const uint32_t j = 4u * gl;
+                    if (EXACT || j + 0 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(o.x));
+                    if (EXACT || j + 1 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(o.y));
+                    if (EXACT || j + 2 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(o.z));
+                    if (EXACT || j + 3 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(o.w));
+                }
+                if (child < a.n) store_row_block(nxt + (size_t)child * nblk + gl, o);
+            }
+            float s;
+            if (ENC == ENC_BITS) {
+#pragma unroll
+                for (uint32_t off = G >> 1; off >= 1u; off >>= 1) iacc += __shfl_xor_sync(0xFFFFFFFFu, iacc, off);
+                s = __uint2float_rn(iacc);
+            } else {
+#pragma unroll
+                for (uint32_t off = G >> 1; off >= 1u; off >>= 1)
+                    facc = __fadd_rn(facc, __shfl_xor_sync(0xFFFFFFFFu, facc, off));
+                s = obj_finalize<OBJ>(facc, a.len);
+            }
+            const float v = __shfl_sync(0xFFFFFFFFu, s, (lane & (CPT - 1u)) << LOGG);
+            if ((lane >> (5 - LOGG)) == tile) my_score = v;
+        }
+        const uint32_t mine = cbase + lane;
+        if (mine < a.n) {
+            a.score_out[mine] = my_score;
+            const unsigned long long k = best_key(my_score, mine);
+            key = k > key ? k : key;
+        }
+        __syncwarp();  // the stage is rewritten two iterations from now
     }
     block_best_commit(key, a.best + a.best_slot, warp_best);
 }

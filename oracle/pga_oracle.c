@@ -251,6 +251,14 @@ static uint32_t tail_mask(unsigned len_bits)
 /* src/pga.cu:177-204 (validation), :107-118 (fill), :81-86 (genes := rand row) */
 opga_pop_t *opga_create_population(opga_t *p, unsigned long size, unsigned genome_len, int encoding)
 {
+	return opga_create_population_on_island(p, size, genome_len, encoding, p->island_base + p->p_count);
+}
+
+/* same, with an explicit global island number (multi-process layouts, where the
+ * local populations of a rank are islands rank, rank + world, ...) */
+opga_pop_t *opga_create_population_on_island(opga_t *p, unsigned long size, unsigned genome_len, int encoding,
+					     uint32_t island)
+{
 	if (p->p_count == OPGA_MAX_POPULATIONS)
 		return NULL;
 	if (genome_len < 4)
@@ -262,7 +270,7 @@ opga_pop_t *opga_create_population(opga_t *p, unsigned long size, unsigned genom
 	q->genome_len = genome_len;
 	q->encoding = encoding;
 	q->row_words = encoding == OPGA_GENES_BITS ? (genome_len + 31) / 32 : genome_len;
-	q->island = p->island_base + p->p_count;
+	q->island = island;
 	q->epoch = 0;
 	size_t words = (size_t)size * q->row_words;
 	q->cur = calloc(words ? words : 1, 4);

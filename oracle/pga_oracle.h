@@ -67,6 +67,8 @@ void opga_set_threads(opga_t *, int nthreads); /* 1 = serial (default) */
 void opga_set_island_base(opga_t *, uint32_t first_global_island);
 void opga_set_quiet(opga_t *, int quiet);
 opga_pop_t *opga_create_population(opga_t *, unsigned long size, unsigned genome_len, int encoding);
+opga_pop_t *opga_create_population_on_island(opga_t *, unsigned long size, unsigned genome_len, int encoding,
+					     uint32_t island);
 void opga_set_objective_function(opga_t *, opga_obj_f);
 void opga_set_builtin_objective(opga_t *, int which);
 void opga_set_mutate_function(opga_t *, opga_mutate_f);

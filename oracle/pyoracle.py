@@ -53,6 +53,7 @@ def lib():
         "opga_set_island_base": (None, [vp, u32]),
         "opga_set_quiet": (None, [vp, i32]),
         "opga_create_population": (vp, [vp, ul, ui, i32]),
+        "opga_create_population_on_island": (vp, [vp, ul, ui, i32, u32]),
         "opga_set_objective_function": (None, [vp, vp]),
         "opga_set_builtin_objective": (None, [vp, i32]),
         "opga_set_mutate_function": (None, [vp, vp]),
@@ -216,8 +217,11 @@ class Oracle:
     def __exit__(self, *a):
         self.close()
 
-    def create_population(self, size, genome_len, encoding=GENES_F32):
-        h = self.L.opga_create_population(self.h, size, genome_len, encoding)
+    def create_population(self, size, genome_len, encoding=GENES_F32, island=None):
+        if island is None:
+            h = self.L.opga_create_population(self.h, size, genome_len, encoding)
+        else:
+            h = self.L.opga_create_population_on_island(self.h, size, genome_len, encoding, island)
         if not h:
             return None
         p = Population(self, h)

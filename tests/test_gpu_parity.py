@@ -200,16 +200,6 @@ def test_rastrigin_shapes(pga, oracle, monkeypatch, length, generic):
     o.close()
 
 
-@pytest.mark.parametrize("policy", [("1", "2"), ("2", "1"), ("1", "0")])
-def test_l2_hints_do_not_change_results(pga, oracle, monkeypatch, policy):
-    monkeypatch.setenv("PGA_L2_LOAD", policy[0])
-    monkeypatch.setenv("PGA_L2_STORE", policy[1])
-    g, o, gp, op = setup_pair(pga, oracle, 5, 5000, 1024, encoding=pg.GENES_BITS, builtin=pg.OBJ_ONEMAX)
-    g.run(5); o.run(5)
-    assert np.array_equal(gp.genes(), op.genes())
-    o.close()
-
-
 def test_onemax_full_size_lockstep(pga, oracle):
     # config 2 at full size: 2^20 x 1024 bits, three lock-step generations
     n, bits = 1 << 20, 1024
