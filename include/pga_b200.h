@@ -29,6 +29,7 @@ extern "C" {
 #define PGAX_ERANGE (-2)   /* size beyond a documented limit */
 #define PGAX_ENOSYS (-3)   /* combination not supported (e.g. hooks on packed bits) */
 #define PGAX_ENCCL (-4)    /* NCCL library not loadable */
+#define PGAX_ECUDA (-5)    /* a CUDA call failed (only from entry points that say so) */
 
 enum pgax_gene_encoding {
 	PGAX_GENES_F32 = 0, /* libpga's `gene`: one float per gene */
@@ -106,6 +107,30 @@ int pgax_get_best_words(pga_t *, population_t *, uint32_t *row_out);
  * engine's total order (higher score first, then lower index; NaN last), listed
  * in ascending index order.  host_indices receives min(k, size) entries. */
 int pgax_select_top(pga_t *, population_t *, unsigned long k, int worst, uint32_t *host_indices);
+
+/* No counterpart in the reference.  pgax_select_top for callers that cannot let
+ * the library allocate: a process whose GPU memory belongs entirely to its own
+ * pool, or a loop that cannot take the device-wide stall of cudaMalloc/cudaFree.
+ * It needs no solver and no population: `dev_scores` (n floats) and `dev_indices`
+ * (room for min(k, n) indices) are DEVICE pointers supplied by the caller, and the
+ * working memory is a fixed 66 KB array inside the library image, held by every
+ * GPU that loads the library until the process exits.  Same result and order as
+ * pgax_select_top.  Rules:
+ *   - n may not exceed PGAX_NOALLOC_MAX_INDIVIDUALS; larger inputs return
+ *     PGAX_ERANGE with a message on stderr and launch nothing;
+ *   - the work is queued on `cuda_stream` (a cudaStream_t, NULL = default stream)
+ *     and the call returns without waiting; the indices are valid once the stream
+ *     has drained;
+ *   - the FIRST call on each device also looks up the array's device address
+ *     (cudaGetSymbolAddress) with that device current: make that first call
+ *     before any stream capture begins;
+ *   - all calls on a device share the one array: calls whose kernels could overlap
+ *     on the GPU (two streams, two threads) race on it and must be serialised by
+ *     the caller.  It never calls cudaMalloc, cudaFree or any allocating routine.
+ * Returns PGAX_OK, PGAX_EINVAL (NULL pointer), PGAX_ERANGE or PGAX_ECUDA. */
+#define PGAX_NOALLOC_MAX_INDIVIDUALS (1u << 24)
+int pgax_select_top_noalloc(const float *dev_scores, unsigned long n, unsigned long k, int worst,
+			    uint32_t *dev_indices, void *cuda_stream);
 
 int pgax_set_topology(pga_t *, enum pgax_topology);
 /* Generations between choosing emigrants and inserting them at the destination

@@ -61,6 +61,7 @@ SIGNATURES = {
     "pgax_best": (_i32, [_vp, _vp, _vp, _vp]),
     "pgax_get_best_words": (_i32, [_vp, _vp, _vp]),
     "pgax_select_top": (_i32, [_vp, _vp, _ul, _i32, _vp]),
+    "pgax_select_top_noalloc": (_i32, [_vp, _ul, _ul, _i32, _vp, _vp]),
     "pgax_set_topology": (_i32, [_vp, _i32]),
     "pgax_set_migration_delay": (_i32, [_vp, _ui]),
     "pgax_migration_count": (_ul, [_ul, _f32]),

@@ -747,3 +747,89 @@ extern "C" void pgadev_nccl_recv_inbox(pgadev_ctx* c, pgadev_pop* dst, uint64_t 
 {
     NCE(g_nccl.Recv(dst->inbox, box_words(dst, k), ncclUint32, peer, c->comm, c->side));
 }
+
+// ---- ranking without any allocation ----------------------------------------------------------------
+//
+// pgax_select_top_noalloc: the k best / k worst of a score array, exactly as
+// pgax_select_top computes them, for callers that must not (or cannot) reach the
+// CUDA allocator while they work:
+//   * programs that handed the whole of HBM to their own pool or arena at start-up,
+//     where a cudaMalloc from inside a library either fails or eats into memory the
+//     owner believes it has;
+//   * steady-state loops (one selection per migration, thousands of migrations) that
+//     cannot afford cudaMalloc/cudaFree, because both synchronise the whole device
+//     and stall every other stream for the duration.
+// pgax_select_top sizes its histogram, counters and index list with cudaMalloc on
+// first use.  Here the caller brings the input and the output, and the only other
+// memory the selection needs -- the radix histogram, the running prefix and the
+// per-block counts -- lives in the fixed array below, which is part of the library
+// image: every GPU that loads the library carries these 66 KB until the process ends.
+//
+// The array bounds the problem: at most PGAX_NOALLOC_MAX_INDIVIDUALS scores
+// (2^24, i.e. 8192 blocks of 2048).  Larger inputs are refused, not truncated.
+//
+// `noalloc_scratch` below is a DEVICE object.  In host code its name is only a
+// handle for the runtime, not an address a kernel could dereference, so the device
+// address is looked up once per device with cudaGetSymbolAddress (with that device
+// current) and that pointer is what the kernels receive.
+#define NOALLOC_STATE_BYTES 2048u  /* TopkState, padded */
+#define NOALLOC_MAX_BLOCKS ((PGAX_NOALLOC_MAX_INDIVIDUALS + TOPK_CHUNK - 1u) / TOPK_CHUNK)
+#define NOALLOC_SCRATCH_BYTES (NOALLOC_STATE_BYTES + 2u * NOALLOC_MAX_BLOCKS * 4u)
+static_assert(sizeof(TopkState) <= NOALLOC_STATE_BYTES, "scratch layout");
+
+static __device__ __align__(256) unsigned char noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+#define NOALLOC_MAX_DEVICES 64
+static unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES];  // device address of the array, per device
+static int g_noalloc_sms[NOALLOC_MAX_DEVICES];
+
+extern "C" int pgax_select_top_noalloc(const float* dev_scores, unsigned long n, unsigned long k, int worst,
+                                       uint32_t* dev_indices, void* cuda_stream)
+{
+    if (dev_scores == NULL || dev_indices == NULL) return PGAX_EINVAL;
+    if (n > PGAX_NOALLOC_MAX_INDIVIDUALS) {
+        fprintf(stderr, "libpga: pgax_select_top_noalloc: %lu scores exceed the fixed scratch (limit %u); use pgax_select_top\n", n,
+                (unsigned)PGAX_NOALLOC_MAX_INDIVIDUALS);
+        return PGAX_ERANGE;
+    }
+    if (k > n) k = n;
+    if (k == 0) return PGAX_OK;
+
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= NOALLOC_MAX_DEVICES) return PGAX_ECUDA;
+    if (g_noalloc_ptr[dev] == NULL) {
+        // first call on this device: resolve the array's device address (this is the
+        // set-up step; make this first call before any stream capture begins)
+        void* ptr = NULL;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, noalloc_scratch);
+        if (e != cudaSuccess || ptr == NULL) {
+            fprintf(stderr, "libpga: pgax_select_top_noalloc: cudaGetSymbolAddress failed: %s\n", cudaGetErrorString(e));
+            return PGAX_ECUDA;
+        }
+        int sms = 0;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) return PGAX_ECUDA;
+        g_noalloc_sms[dev] = sms;
+        g_noalloc_ptr[dev] = (unsigned char*)ptr;
+    }
+    unsigned char* base = g_noalloc_ptr[dev];
+    TopkState* st = reinterpret_cast<TopkState*>(base);
+    uint32_t* blk_gt = reinterpret_cast<uint32_t*>(base + NOALLOC_STATE_BYTES);
+    uint32_t* blk_eq = blk_gt + NOALLOC_MAX_BLOCKS;
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    const uint32_t n32 = (uint32_t)n, nb = (uint32_t)((n + TOPK_CHUNK - 1) / TOPK_CHUNK);
+    const int w = worst ? 1 : 0;
+
+    // the array still holds the previous call's histogram, prefix and block counts:
+    // topk_begin clears the histogram and the running state, topk_pick re-clears the
+    // histogram between passes, and topk_count overwrites all nb block counts
+    topk_begin<<<1, 256, 0, s>>>(st, (uint32_t)k);
+    const uint32_t hgrid = grid_for(n, 256, (uint32_t)g_noalloc_sms[dev] * 8u);
+    for (int pass = 3; pass >= 0; --pass) {
+        topk_histogram<<<hgrid, 256, 0, s>>>(dev_scores, n32, w, (uint32_t)pass * 8u, st);
+        topk_pick<<<1, 256, 0, s>>>(st, (uint32_t)pass * 8u);
+    }
+    topk_count<<<nb, TOPK_BLOCK, 0, s>>>(dev_scores, n32, w, st, blk_gt, blk_eq);
+    topk_scan<<<1, 1024, 0, s>>>(blk_gt, blk_eq, nb);
+    topk_emit<<<nb, TOPK_BLOCK, 0, s>>>(dev_scores, n32, w, st, blk_gt, blk_eq, dev_indices);
+    return cudaPeekAtLastError() == cudaSuccess ? PGAX_OK : PGAX_ECUDA;
+}
