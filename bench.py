@@ -40,6 +40,14 @@ WORKLOADS = {
 }
 
 
+KERNELS = {
+    "onemax": "generation_fused_tiled<ENC_BITS, OBJ_ONEMAX, LOGG=2, NB=2, TB=4>",
+    "rastrigin": "generation_fused_tiled<ENC_F32, OBJ_RASTRIGIN, LOGG=5, NB=2, TB=2>",
+    "test1": "generation_hooks<PH_FUSED> (user objective through a device function pointer)",
+    "tsp": "generation_hooks<PH_FUSED> (user objective + crossover through device function pointers)",
+}
+
+
 def genome_bytes(w):
     return w["length"] // 8 if w["bits"] else w["length"] * 4
 
@@ -69,6 +77,13 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.proc, self.lines = index, None, []
+        self.t_begin = self.t_end = None
+
+    def mark_begin(self):
+        self.t_begin = time.time()
+
+    def mark_end(self):
+        self.t_end = time.time()
 
     def start(self):
         try:
@@ -81,7 +96,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
     def stop(self):
         if not self.proc:
@@ -93,7 +108,10 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in self.lines:
+        # samples taken inside the timed region (with 0.15 s slack); if the region was
+        # shorter than one sampling period fall back to everything since the warm-up
+        inside = [l for (t, l) in self.lines if self.t_begin and self.t_end and self.t_begin - 0.15 <= t <= self.t_end + 0.15]
+        for line in (inside or [l for (_, l) in self.lines]):
             f = [x.strip() for x in line.split(",")]
             if len(f) < 7:
                 continue
@@ -207,7 +225,7 @@ def cpu_baseline(w):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="onemax", choices=sorted(WORKLOADS))
@@ -262,27 +280,28 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    sampler.start()
     g.evaluate(pop)
     for _ in range(args.warmup):
         step()
 
     # ---- value: population resident in HBM, CUDA events on the launching stream
-    sampler = ClockSampler(local)
     barrier()
-    sampler.start()
     launches0 = g.kernel_launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kernel_ms = 0.0
     barrier()
+    sampler.mark_begin()
     e0.record(stream)
     for _ in range(args.steps):
         step()
         kernel_ms += g.last_run_ms
     e1.record(stream)
     barrier()
+    sampler.mark_end()
     elapsed_ms = e0.elapsed_time(e1)
     launches = g.kernel_launches - launches0
-    clocks = sampler.stop()
     if distributed:
         t = torch.tensor([elapsed_ms, kernel_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -310,6 +329,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t[0])
     e2e_value = e2e_steps * (args.gens + 1) * w["size"] * world / e2e_s  # +1: the uploaded generation is scored too
+    clocks = sampler.stop()
 
     peak, peak_src = measured_peak()
     gb = genome_bytes(w)
@@ -329,7 +349,7 @@ def main():
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic(args.workload), "kernel": "generation_fast<BITS,FUSED,ONEMAX>" if w["bits"] else "generation kernel",
+                     "traffic": ncu_traffic(args.workload), "kernel": KERNELS[args.workload],
                      "algorithmic_bytes_per_launch": 2 * w["size"] * gb, "avg_launch_ms": kernel_ms / n_launch,
                      "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0},
     }

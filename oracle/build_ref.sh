@@ -1,0 +1,39 @@
+#!/bin/bash
+# Builds, from the reference sources where they lie under /root/reference (nothing
+# is copied into the repository):
+#   oracle/_ref/libpga_ref.a        the reference library itself, for sm_100a
+#   oracle/_ref/ref/test{1,2,3}     the reference's demo programs linked against it
+#   oracle/_ref/dropin/test{1,2,3}  the SAME unmodified demo sources linked against
+#                                   THIS repository's libpga.a (the drop-in check)
+#   oracle/_ref/gen                 the reference's test3 instance generator
+# Only the architecture flag differs from the reference's Makefiles (-arch=sm_20 is
+# rejected by nvcc 12.9; Makefile:2, test/Makefile:2-3).  Outputs are git-ignored but
+# travel to the GPU box.  Test infrastructure, not product.
+set -e
+REF=${REF:-/root/reference}
+HERE="$(cd "$(dirname "$0")" && pwd)"
+ROOT="$(dirname "$HERE")"
+OUT="$HERE/_ref"
+ARCH="-gencode arch=compute_100a,code=sm_100a"
+[ -d "$REF/src" ] || { echo "no reference checkout at $REF; keeping prebuilt oracle/_ref"; exit 0; }
+[ -f "$ROOT/libpga.a" ] || make -C "$ROOT" libpga.a
+mkdir -p "$OUT/ref" "$OUT/dropin" "$OUT/obj"
+
+# the reference library (Makefile:11-17)
+nvcc -dc $ARCH -w -I"$REF/include" "$REF/src/pga.cu" -o "$OUT/obj/pga_ref.o"
+rm -f "$OUT/libpga_ref.a"
+nvcc $ARCH -lib "$OUT/obj/pga_ref.o" -o "$OUT/libpga_ref.a"
+
+i=1
+for t in test test2 test3; do
+    # reference program + reference library
+    nvcc -dc $ARCH -w "$REF/$t/test.cu" -I"$REF/include" -o "$OUT/obj/${t}_ref.o"
+    nvcc $ARCH "$OUT/obj/${t}_ref.o" -o "$OUT/ref/test$i" "$OUT/libpga_ref.a" -lcurand
+    # the same source + this repository's header and archive (test/Makefile:2-3 with -L<repo>)
+    nvcc -dc $ARCH -w "$REF/$t/test.cu" -I"$ROOT/include" -o "$OUT/obj/${t}_dropin.o"
+    nvcc $ARCH "$OUT/obj/${t}_dropin.o" -o "$OUT/dropin/test$i" -L"$ROOT" -lpga -lcurand
+    i=$((i + 1))
+done
+/usr/bin/gcc -O2 -w -o "$OUT/gen" "$REF/test3/gen.c" 2>/dev/null || gcc -O2 -w -o "$OUT/gen" "$REF/test3/gen.c"
+rm -rf "$OUT/obj"
+ls -la "$OUT" "$OUT/ref" "$OUT/dropin"

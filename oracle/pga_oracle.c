@@ -72,6 +72,15 @@ float opga_draw_uniform(uint64_t seed, uint32_t island, uint32_t epoch, uint32_t
 	return word_to_uniform(opga_draw_word(seed, island, epoch, individual, OPGA_STREAM_ROW, j));
 }
 
+/* the four words of Philox block b of a stream */
+static void draw_block_words(uint64_t seed, uint32_t island, uint32_t epoch, uint32_t individual, uint32_t stream,
+			     uint32_t b, uint32_t out[4])
+{
+	uint32_t key[2] = { (uint32_t)seed, (uint32_t)(seed >> 32) };
+	uint32_t ctr[4] = { b, individual, epoch, (stream << 24) | (island & 0xFFFFFFu) };
+	opga_philox4x32_10(ctr, key, out);
+}
+
 /* the four uniforms of Philox block b of an individual's rand row */
 static void rand_block(uint64_t seed, uint32_t island, uint32_t epoch, uint32_t individual, uint32_t b, float out[4])
 {
@@ -349,9 +358,11 @@ void opga_crossover(opga_t *p, opga_pop_t *q)
 		const uint32_t *p2 = q->cur + (size_t)b * q->row_words;
 		uint32_t *c = q->nxt + (size_t)i * q->row_words;
 		if (q->encoding == OPGA_GENES_BITS) {
+			uint32_t m[4];
 			for (unsigned w = 0; w < q->row_words; ++w) {
-				uint32_t m = opga_draw_word(p->seed, q->island, q->epoch, (uint32_t)i, OPGA_STREAM_MASK, w);
-				c[w] = (p1[w] & m) | (p2[w] & ~m);
+				if ((w & 3) == 0) /* one Philox block yields four mask words */
+					draw_block_words(p->seed, q->island, q->epoch, (uint32_t)i, OPGA_STREAM_MASK, w >> 2, m);
+				c[w] = (p1[w] & m[w & 3]) | (p2[w] & ~m[w & 3]);
 			}
 		} else if (p->crossover) {
 			float *rnd = malloc(sizeof(float) * q->genome_len);

@@ -1,0 +1,83 @@
+"""The reference's own demo programs, compiled UNCHANGED against this repository's
+pga.h and libpga.a (oracle/build_ref.sh; link line of test/Makefile:3), run on the GPU.
+
+The binaries are built in the development container (the reference checkout does not
+exist on the GPU box) and travel in oracle/_ref/.  Their only output is what the
+reference prints: the best score from pga_get_best (src/pga.cu:230) and, for test2 /
+test3, the decoded best genome.  With PGA_SEED fixed the score must equal the oracle's.
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+DROPIN = os.path.join(ROOT, "oracle", "_ref", "dropin")
+REF = os.path.join(ROOT, "oracle", "_ref", "ref")
+
+
+def run(path, seed, stdin=None):
+    if not os.path.exists(path):
+        pytest.skip(f"{path} not built (run oracle/build_ref.sh where /root/reference exists)")
+    env = dict(os.environ, PGA_SEED=str(seed))
+    r = subprocess.run([path], input=stdin, capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0, r.stderr
+    return r.stdout
+
+
+def test_dropin_test1_matches_oracle(oracle):
+    # test/test.cu:37-45: 40000 x 100, sum objective, 100 generations, prints the best score
+    out = run(os.path.join(DROPIN, "test1"), 42)
+    o = oracle.Oracle(42, threads=8)
+    p = o.create_population(40000, 100)
+    o.set_objective_hook("sum_obj")
+    o.run(100)
+    _, best = o.best_index(p)
+    o.close()
+    assert out == "%f\n" % best
+    assert 90.0 < best <= 100.0
+
+
+def test_dropin_test2_matches_oracle(oracle):
+    # test2/test.cu:43-58: knapsack, 100 x 6, 5 generations; prints score then item counts
+    out = run(os.path.join(DROPIN, "test2"), 7).split("\n")
+    o = oracle.Oracle(7)
+    p = o.create_population(100, 6)
+    o.set_objective_hook("knapsack_obj")
+    o.run(5)
+    idx, best = o.best_index(p)
+    row = p.genes()[idx]
+    o.close()
+    assert out[0] == "%f" % best
+    assert out[1].split() == [str(int(v * 2)) for v in row]
+
+
+def test_dropin_test3_matches_oracle(oracle, tsp_matrix):
+    # test3/test.cu:69-110: instance on stdin, 1000 x 100, custom crossover, 1000 generations
+    with open(os.path.join(ROOT, "tests", "golden", "tsp100.txt")) as f:
+        instance = f.read()
+    out = run(os.path.join(DROPIN, "test3"), 3, stdin=instance)
+    o = oracle.Oracle(3, threads=8)
+    p = o.create_population(1000, 100)
+    o.set_objective_hook("tsp_obj")
+    o.set_crossover_hook("tsp_crossover")
+    o.tsp_load(tsp_matrix)
+    o.run(1000)
+    idx, best = o.best_index(p)
+    row = p.genes()[idx]
+    o.close()
+    lines = out.split("\n")
+    assert lines[0] == "%f" % best
+    tour = [int(np.float32(v) * np.float32(100)) for v in row]
+    assert out.replace("\nHERE", "").split("\n")[1].split() == [str(c) for c in tour]
+
+
+def test_reference_itself_runs_on_this_gpu():
+    # courtesy check of the reference rebuilt for sm_100a: time-seeded, so only the
+    # shape of its output can be asserted (one "%f" line, at most the optimum 100.0)
+    out = run(os.path.join(REF, "test1"), 0)
+    v = float(out.strip().split("\n")[0])
+    assert 50.0 < v <= 100.0
