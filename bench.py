@@ -232,6 +232,7 @@ def main():
     ap.add_argument("--gens", type=int, default=100, help="generations per step")
     ap.add_argument("--size", type=int, default=0, help="override the population size")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--islands", type=int, default=1, help="islands per GPU (BASELINE config 5: 8 islands over N GPUs)")
     ap.add_argument("--migrate-every", type=int, default=10)
     ap.add_argument("--migrate-pct", type=float, default=1.0)
     args = ap.parse_args()
@@ -266,11 +267,14 @@ def main():
     if distributed:
         islands.rendezvous(g, dist)
         g.set_topology(pg.TOPO_RING)
-    pop = g.create_population(w["size"], w["length"], encoding=enc)
+    pops = [g.create_population(w["size"], w["length"], encoding=enc) for _ in range(args.islands)]
+    pop = pops[0]
     configure(pg, g, w)
+    if args.islands > 1 and not distributed:
+        g.set_topology(pg.TOPO_RING)
 
     def step():
-        if distributed:
+        if distributed or args.islands > 1:
             g.run_islands(args.gens, args.migrate_every, args.migrate_pct)
         else:
             g.run(args.gens)
@@ -282,7 +286,7 @@ def main():
 
     sampler = ClockSampler(local)
     sampler.start()
-    g.evaluate(pop)
+    g.evaluate_all()
     for _ in range(args.warmup):
         step()
 
@@ -306,7 +310,7 @@ def main():
         t = torch.tensor([elapsed_ms, kernel_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         elapsed_ms, kernel_ms = float(t[0]), float(t[1])
-    evals = args.steps * args.gens * w["size"] * world
+    evals = args.steps * args.gens * w["size"] * world * args.islands
     value = evals / (elapsed_ms * 1e-3)
 
     # ---- e2e: initial population from pinned host memory, best individual back, every step
@@ -328,21 +332,22 @@ def main():
         t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t[0])
-    e2e_value = e2e_steps * (args.gens + 1) * w["size"] * world / e2e_s  # +1: the uploaded generation is scored too
+    # +1: the uploaded generation is scored too (only island 0 is re-uploaded per step)
+    e2e_value = e2e_steps * (args.gens * args.islands + 1) * w["size"] * world / e2e_s
     clocks = sampler.stop()
 
     peak, peak_src = measured_peak()
     gb = genome_bytes(w)
-    n_launch = args.steps * args.gens
+    n_launch = args.steps * args.gens * args.islands
     achieved = (2.0 * w["size"] * gb) / (kernel_ms * 1e-3 / n_launch) / 1e9  # algorithmic GB/s of the fused kernel
     line = {
         "metric": "genome-evaluations/sec", "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32" if w["bits"] else "f32", "data": "synthetic",
         "generations_per_sec": args.steps * args.gens / (elapsed_ms * 1e-3),
-        "config": {"workload": w["label"], "generations_per_step": args.gens, "islands": world, "seed": 42,
+        "config": {"workload": w["label"], "generations_per_step": args.gens, "islands": world * args.islands, "islands_per_gpu": args.islands, "seed": 42,
                    "operators": "tournament-2, uniform crossover, p=0.01 single-gene mutation",
-                   "migration": f"ring, top {args.migrate_pct}% every {args.migrate_every} generations over NCCL" if distributed else "none (single island)",
+                   "migration": f"ring, top {args.migrate_pct}% every {args.migrate_every} generations over NCCL" if (distributed or args.islands > 1) else "none (single island)",
                    "l2": "inputs larger than L2: two generations of the population = %.0f MiB vs 126 MB" % (2 * w["size"] * gb / 2 ** 20)},
         "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "what": "upload population (pinned host) + pga_run/pga_run_islands + pga_get_best, wall clock"},

@@ -39,7 +39,8 @@ struct pgadev_ctx {
     int device;
     int sm_count;
     cudaStream_t own_stream, stream, side;
-    cudaEvent_t ev_main, ev_side, t0, t1;
+    int route_side;  // ranking and packing go to the side stream (emigrant selection overlaps the next generation)
+    cudaEvent_t ev_main, ev_side, ev_packed, t0, t1;
     unsigned long long launches;
     ncclComm_t comm;
     int hook_threads;  // $PGA_HOOK_THREADS override, 0 = automatic
@@ -65,8 +66,8 @@ struct pgadev_pop {
     int32_t* sel;
     int capture;
     // ranking scratch
-    TopkState* topk;
-    uint32_t *blk_gt, *blk_eq;
+    TopkState2* topk[2];  // one set per index list: emigrants may be ranked on the side stream
+    uint32_t *blk_gt[2], *blk_eq[2];
     uint32_t nb;
     uint32_t* idx[2];
     uint64_t idx_cap[2];
@@ -104,6 +105,7 @@ extern "C" pgadev_ctx* pgadev_ctx_create(void)
     c->stream = c->own_stream;
     CCE(cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming));
     CCE(cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming));
+    CCE(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
     CCE(cudaEventCreate(&c->t0));
     CCE(cudaEventCreate(&c->t1));
     const char* ht = getenv("PGA_HOOK_THREADS");
@@ -126,6 +128,7 @@ extern "C" void pgadev_ctx_destroy(pgadev_ctx* c)
     nccl_destroy(c);
     CCE(cudaEventDestroy(c->ev_main));
     CCE(cudaEventDestroy(c->ev_side));
+    CCE(cudaEventDestroy(c->ev_packed));
     CCE(cudaEventDestroy(c->t0));
     CCE(cudaEventDestroy(c->t1));
     CCE(cudaStreamDestroy(c->own_stream));
@@ -194,9 +197,11 @@ extern "C" void pgadev_pop_destroy(pgadev_ctx* c, pgadev_pop* p)
     }
     if (p->best) CCE(cudaFree(p->best));
     if (p->sel) CCE(cudaFree(p->sel));
-    if (p->topk) CCE(cudaFree(p->topk));
-    if (p->blk_gt) CCE(cudaFree(p->blk_gt));
-    if (p->blk_eq) CCE(cudaFree(p->blk_eq));
+    for (int i = 0; i < 2; ++i) {
+        if (p->topk[i]) CCE(cudaFree(p->topk[i]));
+        if (p->blk_gt[i]) CCE(cudaFree(p->blk_gt[i]));
+        if (p->blk_eq[i]) CCE(cudaFree(p->blk_eq[i]));
+    }
     if (p->outbox) CCE(cudaFree(p->outbox));
     if (p->inbox) CCE(cudaFree(p->inbox));
     free(p);
@@ -311,25 +316,25 @@ static int launch_tiled_inst(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
     return exact ? launch_tiled_one<ENC, OBJ, LOGG, NB, true>(c, p, a) : launch_tiled_one<ENC, OBJ, LOGG, NB, false>(c, p, a);
 }
 
-// small rows (<= 128 B): per-warp cp.async pipeline through shared memory.  Slower
-// than the register-tiled kernel on B200 (95 vs 73 us per OneMax generation), kept
-// selectable with $PGA_STAGED=1 as the measured alternative.
-template <int ENC, int OBJ, int LOGG, bool EXACT, int WARPS>
+// small rows (32..128 B): per-warp cp.async pipeline through shared memory,
+// selectable with $PGA_STAGED=<blocks per SM target> (experiment)
+template <int ENC, int OBJ, int LOGG, bool EXACT, int MINB>
 static int launch_staged_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
-    constexpr size_t smem = (size_t)WARPS * 2u * 64u * (16u << LOGG);
+    constexpr int WARPS = 4;
+    constexpr size_t smem = (size_t)WARPS * 2u * 32u * (16u << LOGG);
     static int configured_for = -1;
     static int blocks_per_sm = 1;
     if (configured_for != c->device) {
-        CCE(cudaFuncSetAttribute(generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)smem));
-        CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS>,
+        CCE(cudaFuncSetAttribute(generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS, MINB>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS, MINB>,
                                                           WARPS * 32, smem));
         if (blocks_per_sm < 1) blocks_per_sm = 1;
         configured_for = c->device;
     }
     const uint32_t grid = grid_for(p->n, WARPS * 32u, (uint32_t)(c->sm_count * blocks_per_sm));
-    generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS><<<grid, WARPS * 32, smem, c->stream>>>(a);
+    generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS, MINB><<<grid, WARPS * 32, smem, c->stream>>>(a);
     LAUNCH_CHECK(c);
     return 0;
 }
@@ -338,11 +343,13 @@ template <int ENC, int OBJ>
 static int launch_staged(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
     const uint32_t nblk = p->stride >> 2, G = p->group;
-    if (!c->staged || c->force_generic || nblk > G || G > 8) return 1;
+    if (!c->staged || c->force_generic || nblk > G || G > 8 || G < 2) return 1;
     const bool exact = nblk == G && (ENC == ENC_BITS || p->len == p->stride);
-#define ST(L) return exact ? launch_staged_one<ENC, OBJ, L, true, 4>(c, p, a) : launch_staged_one<ENC, OBJ, L, false, 4>(c, p, a)
+#define ST(L)                                                                                                       \
+    if (c->staged >= 7) return exact ? launch_staged_one<ENC, OBJ, L, true, 7>(c, p, a) : launch_staged_one<ENC, OBJ, L, false, 7>(c, p, a); \
+    if (c->staged >= 6) return exact ? launch_staged_one<ENC, OBJ, L, true, 6>(c, p, a) : launch_staged_one<ENC, OBJ, L, false, 6>(c, p, a); \
+    return exact ? launch_staged_one<ENC, OBJ, L, true, 4>(c, p, a) : launch_staged_one<ENC, OBJ, L, false, 4>(c, p, a)
     switch (G) {
-        case 1: ST(0);
         case 2: ST(1);
         case 4: ST(2);
         default: ST(3);
@@ -569,33 +576,39 @@ static void ensure_index_list(pgadev_ctx* c, pgadev_pop* p, int slot, uint64_t k
     p->idx_cap[slot] = k;
 }
 
+static cudaStream_t work_stream(pgadev_ctx* c) { return c->route_side ? c->side : c->stream; }
+
+extern "C" void pgadev_route_to_side(pgadev_ctx* c, int on) { c->route_side = on; }
+
 extern "C" void pgadev_select_top(pgadev_ctx* c, pgadev_pop* p, uint64_t k, int worst, int slot)
 {
     if (k == 0 || p->n == 0) return;
     if (k > p->n) k = p->n;
-    if (!p->topk) {
+    if (!p->topk[slot]) {
         p->nb = (uint32_t)((p->n + TOPK_CHUNK - 1) / TOPK_CHUNK);
-        CCE(cudaMalloc((void**)&p->topk, sizeof(TopkState)));
-        CCE(cudaMalloc((void**)&p->blk_gt, (size_t)p->nb * sizeof(uint32_t)));
-        CCE(cudaMalloc((void**)&p->blk_eq, (size_t)p->nb * sizeof(uint32_t)));
+        CCE(cudaMalloc((void**)&p->topk[slot], sizeof(TopkState2)));
+        CCE(cudaMemset(p->topk[slot], 0, sizeof(TopkState2)));
+        CCE(cudaMalloc((void**)&p->blk_gt[slot], (size_t)p->nb * sizeof(uint32_t)));
+        CCE(cudaMalloc((void**)&p->blk_eq[slot], (size_t)p->nb * sizeof(uint32_t)));
     }
     ensure_index_list(c, p, slot, k);
+    cudaStream_t s = work_stream(c);
+    TopkState2* st = p->topk[slot];
+    uint32_t *bg = p->blk_gt[slot], *be = p->blk_eq[slot];
     const float* score = p->score[p->sidx];
     const uint32_t n = (uint32_t)p->n;
-    topk_begin<<<1, 256, 0, c->stream>>>(p->topk, (uint32_t)k);
+    // five launches: three radix passes (the last block of each picks the digit), the
+    // per-block counts (the last block scans them), the stable compaction
+    const uint32_t hgrid = grid_for(p->n, 256 * 4, (uint32_t)c->sm_count * 4u);
+    topk2_histogram<21, 11><<<hgrid, 256, 0, s>>>(score, n, worst, (uint32_t)k, st);
     LAUNCH_CHECK(c);
-    const uint32_t hgrid = grid_for(p->n, 256, (uint32_t)c->sm_count * 8u);
-    for (int pass = 3; pass >= 0; --pass) {
-        topk_histogram<<<hgrid, 256, 0, c->stream>>>(score, n, worst, (uint32_t)pass * 8u, p->topk);
-        LAUNCH_CHECK(c);
-        topk_pick<<<1, 256, 0, c->stream>>>(p->topk, (uint32_t)pass * 8u);
-        LAUNCH_CHECK(c);
-    }
-    topk_count<<<p->nb, TOPK_BLOCK, 0, c->stream>>>(score, n, worst, p->topk, p->blk_gt, p->blk_eq);
+    topk2_histogram<10, 11><<<hgrid, 256, 0, s>>>(score, n, worst, (uint32_t)k, st);
     LAUNCH_CHECK(c);
-    topk_scan<<<1, 1024, 0, c->stream>>>(p->blk_gt, p->blk_eq, p->nb);
+    topk2_histogram<0, 10><<<hgrid, 256, 0, s>>>(score, n, worst, (uint32_t)k, st);
     LAUNCH_CHECK(c);
-    topk_emit<<<p->nb, TOPK_BLOCK, 0, c->stream>>>(score, n, worst, p->topk, p->blk_gt, p->blk_eq, p->idx[slot]);
+    topk2_count_scan<<<p->nb, TOPK_BLOCK, 0, s>>>(score, n, worst, st, bg, be, p->nb);
+    LAUNCH_CHECK(c);
+    topk2_emit<<<p->nb, TOPK_BLOCK, 0, s>>>(score, n, worst, st, bg, be, p->idx[slot]);
     LAUNCH_CHECK(c);
 }
 
@@ -627,7 +640,7 @@ extern "C" void pgadev_pack_emigrants(pgadev_ctx* c, pgadev_pop* p, uint64_t k)
 {
     ensure_boxes(c, p, k);
     const uint32_t grid = grid_for(k * (p->stride >> 2), 256, (uint32_t)c->sm_count * 8u);
-    pack_rows<<<grid, 256, 0, c->stream>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[0], (uint32_t)k, p->stride, p->outbox);
+    pack_rows<<<grid, 256, 0, work_stream(c)>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[0], (uint32_t)k, p->stride, p->outbox);
     LAUNCH_CHECK(c);
 }
 
@@ -648,6 +661,11 @@ extern "C" void pgadev_side_after_main(pgadev_ctx* c)
     CCE(cudaEventRecord(c->ev_main, c->stream));
     CCE(cudaStreamWaitEvent(c->side, c->ev_main, 0));
 }
+
+// the emigrants of this exchange have left the population buffers (side stream)
+extern "C" void pgadev_mark_packed(pgadev_ctx* c) { CCE(cudaEventRecord(c->ev_packed, c->side)); }
+// the main stream may overwrite those buffers only after that
+extern "C" void pgadev_main_wait_packed(pgadev_ctx* c) { CCE(cudaStreamWaitEvent(c->stream, c->ev_packed, 0)); }
 
 extern "C" void pgadev_main_after_side(pgadev_ctx* c)
 {

@@ -88,6 +88,12 @@ void pgadev_pack_emigrants(pgadev_ctx *, pgadev_pop *, uint64_t k);
 void pgadev_transfer_local(pgadev_ctx *, pgadev_pop *src, pgadev_pop *dst, uint64_t k);
 /* overwrite the k victims listed in slot 1 with the inbox (rows + scores) */
 void pgadev_unpack_immigrants(pgadev_ctx *, pgadev_pop *, uint64_t k);
+/* route the following select_top / pack_emigrants calls to the side stream (1) or
+ * back to the main stream (0) */
+void pgadev_route_to_side(pgadev_ctx *, int on);
+/* record "emigrants packed" on the side stream / make the main stream wait for it */
+void pgadev_mark_packed(pgadev_ctx *);
+void pgadev_main_wait_packed(pgadev_ctx *);
 /* side stream waits for the main stream / main stream waits for the side stream */
 void pgadev_side_after_main(pgadev_ctx *);
 void pgadev_main_after_side(pgadev_ctx *);

@@ -53,6 +53,7 @@ struct pga { /* reference: src/pga.cu:48-56 */
 struct exchange {
 	int active;
 	unsigned land_gen;
+	unsigned start_gen;
 	uint64_t k_in[MAX_POPULATIONS];         /* immigrants per local island */
 };
 
@@ -522,6 +523,10 @@ static void exchange_start(pga_t *p, struct exchange *ex, float pct)
 	for (unsigned s = 0; s < K; ++s)
 		pgadev_reserve_boxes(p->dev, p->populations[s]->dev, pgax_migration_count(p->populations[s]->size, pct));
 
+	/* emigrants are ranked and packed on the side stream: they only read the
+	 * generation that just finished, so this overlaps the next generation */
+	pgadev_side_after_main(p->dev);
+	pgadev_route_to_side(p->dev, 1);
 	uint64_t k_out[MAX_POPULATIONS];
 	memset(k_out, 0, sizeof(k_out));
 	for (int t = 0; t < count; ++t) {
@@ -540,7 +545,8 @@ static void exchange_start(pga_t *p, struct exchange *ex, float pct)
 			pgadev_pack_emigrants(p->dev, src->dev, k);
 		}
 	}
-	pgadev_side_after_main(p->dev);
+	pgadev_route_to_side(p->dev, 0);
+	pgadev_mark_packed(p->dev);
 
 	/* the plan lists transfers in ascending source order on every rank, so the
 	 * messages between one pair of ranks are posted in the same order on both */
@@ -643,12 +649,16 @@ void pga_run_islands(pga_t *p, unsigned n, unsigned m, float pct) /* stub: src/p
 	ensure_scores(p);
 	pgadev_timer_start(p->dev);
 	for (unsigned g = 1; g <= n; ++g) {
+		/* generation start+2 overwrites the buffers the emigrants are packed from */
+		if (ex.active && g == ex.start_gen + 2)
+			pgadev_main_wait_packed(p->dev);
 		for (unsigned s = 0; s < p->p_count; ++s)
 			generation_async(p, p->populations[s]);
 		if (ex.active && ex.land_gen == g)
 			exchange_finish(p, &ex);
 		if (m && g % m == 0 && g + p->delay <= n && total > 1 && !ex.active) {
 			exchange_start(p, &ex, pct);
+			ex.start_gen = g;
 			ex.land_gen = g + p->delay;
 			if (p->delay == 0)
 				exchange_finish(p, &ex);

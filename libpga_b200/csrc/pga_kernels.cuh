@@ -519,9 +519,9 @@ __global__ void __launch_bounds__(256, MINB) generation_fused_tiled(const __grid
 // Here every warp runs its own three-deep software pipeline over its iterations
 // (32 children each):
 //     iteration i+2 : Philox block 0 + the four score gathers are issued
-//     iteration i+1 : tournaments resolved, both parent rows of all 32 children
-//                     copied global -> shared with 16-byte cp.async (LDGSTS),
-//                     8 KB in flight per warp, no registers held
+//     iteration i+1 : tournaments resolved, both parent rows copied global -> shared
+//                     with 16-byte cp.async (LDGSTS), half an iteration at a time,
+//                     no registers held
 //     iteration i   : rows read back from shared memory, crossover mask drawn,
 //                     child mutated, scored, stored
 // Measured on B200 (scripts/microbench_stage.cu): for 128-byte rows one TMA bulk
@@ -561,10 +561,15 @@ __device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
 }
 
-template <int ENC, int OBJ, int LOGG, bool EXACT, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) generation_fused_staged(const __grid_constant__ GenArgs a)
+// A warp's iteration is split in two halves of 16 children; each half owns one 4 KB
+// (for 128-byte rows) stage of shared memory, so 8 KB per warp keep ~24 warps per SM
+// resident with one half always in flight while the other is consumed.
+template <int ENC, int OBJ, int LOGG, bool EXACT, int WARPS, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB) generation_fused_staged(const __grid_constant__ GenArgs a)
 {
-    constexpr uint32_t G = 1u << LOGG, CPT = 32u / G, ROW = G * 16u, STAGE = 64u * ROW;
+    constexpr uint32_t G = 1u << LOGG, CPT = 32u / G, ROW = G * 16u, STAGE = 32u * ROW;  // 16 children x 2 parents
+    constexpr uint32_t HT = G / 2u;  // tiles per half
+    static_assert(LOGG >= 1 && LOGG <= 3, "staged kernel: rows of 32..128 bytes");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ unsigned long long warp_best[WARPS];
     const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
@@ -582,53 +587,38 @@ __global__ void __launch_bounds__(WARPS * 32) generation_fused_staged(const __gr
     const uint32_t iters = gwarp < total ? (total - gwarp + nwarps - 1u) / nwarps : 0u;
     unsigned long long key = 0ull;
 
-    // resolve the tournaments of iteration `it` and start its 64 row copies
-    auto issue = [&](const SelDraw& d, uint32_t it) {
-        const uint32_t mine = (gwarp + it * nwarps) * 32u + lane;
-        const uint32_t p1 = d.s0 < d.s1 ? d.c1 : d.c0;  // src/pga.cu:286-290
-        const uint32_t p2 = d.s2 < d.s3 ? d.c3 : d.c2;
-        if (a.sel && mine < a.n) { a.sel[2 * (size_t)mine] = (int32_t)p1; a.sel[2 * (size_t)mine + 1] = (int32_t)p2; }
-        unsigned char* st = my + (it & 1u) * STAGE;
+    // copy both parent rows of the 16 children of half `h` into stage h
+    auto issue_half = [&](uint32_t p1, uint32_t p2, uint32_t h) {
+        unsigned char* st = my + h * STAGE;
 #pragma unroll
-        for (uint32_t tile = 0; tile < G; ++tile) {
-            const uint32_t c = tile * CPT + grp;
+        for (uint32_t t = 0; t < HT; ++t) {
+            const uint32_t c = (h * HT + t) * CPT + grp;  // child slot 0..31 of the iteration
             const uint32_t q1 = __shfl_sync(0xFFFFFFFFu, p1, c);
             const uint32_t q2 = __shfl_sync(0xFFFFFFFFu, p2, c);
             if (in_row) {
-                cp_async_16(st + (c * 2u + 0u) * ROW + gl * 16u, cur + (size_t)q1 * nblk + gl);
-                cp_async_16(st + (c * 2u + 1u) * ROW + gl * 16u, cur + (size_t)q2 * nblk + gl);
+                const uint32_t slot = (t * CPT + grp) * 2u;  // row slot inside the stage
+                cp_async_16(st + (slot + 0u) * ROW + gl * 16u, cur + (size_t)q1 * nblk + gl);
+                cp_async_16(st + (slot + 1u) * ROW + gl * 16u, cur + (size_t)q2 * nblk + gl);
             }
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
+    auto resolve = [&](const SelDraw& d, uint32_t it, uint32_t& p1, uint32_t& p2) {
+        const uint32_t mine = (gwarp + it * nwarps) * 32u + lane;
+        p1 = d.s0 < d.s1 ? d.c1 : d.c0;  // src/pga.cu:286-290
+        p2 = d.s2 < d.s3 ? d.c3 : d.c2;
+        if (a.sel && mine < a.n) { a.sel[2 * (size_t)mine] = (int32_t)p1; a.sel[2 * (size_t)mine + 1] = (int32_t)p2; }
+    };
 
-    SelDraw d1, d2;  // iteration i+1 (scores resolved at issue), iteration i+2 (gathers in flight)
-    uint32_t mut_idx0 = 0, mut_val0 = 0, any0 = 0;  // mutation data of the iteration being consumed
-    uint32_t mut_idx1 = 0, mut_val1 = 0, any1 = 0;
-    if (iters > 0) {
-        d1 = sel_begin<ENC>(a, gwarp * 32u + lane);
-        issue(d1, 0);
-        mut_idx1 = d1.m_idx; mut_val1 = d1.m_val; any1 = __ballot_sync(0xFFFFFFFFu, d1.m_on);
-    }
-    if (iters > 1) d2 = sel_begin<ENC>(a, (gwarp + nwarps) * 32u + lane);
-
-    for (uint32_t it = 0; it < iters; ++it) {
-        mut_idx0 = mut_idx1; mut_val0 = mut_val1; any0 = any1;
-        if (it + 1u < iters) {
-            issue(d2, it + 1u);
-            mut_idx1 = d2.m_idx; mut_val1 = d2.m_val; any1 = __ballot_sync(0xFFFFFFFFu, d2.m_on);
-            if (it + 2u < iters) d2 = sel_begin<ENC>(a, (gwarp + (it + 2u) * nwarps) * 32u + lane);
-            asm volatile("cp.async.wait_group 1;" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-        }
-        __syncwarp();
-
+    float my_score = 0.f;
+    uint32_t mut_idx0 = 0, mut_val0 = 0, any0 = 0;
+    // crossover, mutation and scoring of half `h` of iteration `it`, from stage h
+    auto consume_half = [&](uint32_t it, uint32_t h) {
         const uint32_t cbase = (gwarp + it * nwarps) * 32u;
-        const unsigned char* st = my + (it & 1u) * STAGE;
-        float my_score = 0.f;
+        const unsigned char* st = my + h * STAGE;
 #pragma unroll
-        for (uint32_t tile = 0; tile < G; ++tile) {
+        for (uint32_t t = 0; t < HT; ++t) {
+            const uint32_t tile = h * HT + t;
             const uint32_t c = tile * CPT + grp;
             const uint32_t child = cbase + c;
             uint32_t c_idx = 0, c_val = 0;
@@ -641,8 +631,9 @@ __global__ void __launch_bounds__(WARPS * 32) generation_fused_staged(const __gr
             float facc = 0.f;
             uint32_t iacc = 0;
             if (in_row) {
-                const uint4 xx = *reinterpret_cast<const uint4*>(st + (c * 2u + 0u) * ROW + gl * 16u);
-                const uint4 yy = *reinterpret_cast<const uint4*>(st + (c * 2u + 1u) * ROW + gl * 16u);
+                const uint32_t slot = (t * CPT + grp) * 2u;
+                const uint4 xx = *reinterpret_cast<const uint4*>(st + (slot + 0u) * ROW + gl * 16u);
+                const uint4 yy = *reinterpret_cast<const uint4*>(st + (slot + 1u) * ROW + gl * 16u);
                 uint4 o;
                 if (ENC == ENC_BITS) {
                     const uint4 m = draw_block(a.draw, STREAM_MASK, child, gl);
@@ -692,14 +683,51 @@ __global__ void __launch_bounds__(WARPS * 32) generation_fused_staged(const __gr
             const float v = __shfl_sync(0xFFFFFFFFu, s, (lane & (CPT - 1u)) << LOGG);
             if ((lane >> (5 - LOGG)) == tile) my_score = v;
         }
-        const uint32_t mine = cbase + lane;
+    };
+
+    SelDraw dn;  // the iteration after the current one: its score gathers are in flight
+    uint32_t p1n = 0, p2n = 0, mut_idx1 = 0, mut_val1 = 0, any1 = 0;
+    if (iters > 0) {
+        dn = sel_begin<ENC>(a, gwarp * 32u + lane);
+        resolve(dn, 0, p1n, p2n);
+        mut_idx0 = dn.m_idx; mut_val0 = dn.m_val; any0 = __ballot_sync(0xFFFFFFFFu, dn.m_on);
+        issue_half(p1n, p2n, 0);
+        issue_half(p1n, p2n, 1);
+        if (iters > 1) dn = sel_begin<ENC>(a, (gwarp + nwarps) * 32u + lane);
+    }
+
+    for (uint32_t it = 0; it < iters; ++it) {
+        const bool more = it + 1u < iters;
+        // half 0
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        __syncwarp();
+        consume_half(it, 0);
+        __syncwarp();
+        if (more) {
+            resolve(dn, it + 1u, p1n, p2n);
+            mut_idx1 = dn.m_idx; mut_val1 = dn.m_val; any1 = __ballot_sync(0xFFFFFFFFu, dn.m_on);
+            issue_half(p1n, p2n, 0);
+        } else {
+            asm volatile("cp.async.commit_group;" ::: "memory");  // keep the group count uniform
+        }
+        // half 1
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        __syncwarp();
+        consume_half(it, 1);
+        __syncwarp();
+        if (more) issue_half(p1n, p2n, 1);
+        else asm volatile("cp.async.commit_group;" ::: "memory");
+
+        const uint32_t mine = (gwarp + it * nwarps) * 32u + lane;
         if (mine < a.n) {
             a.score_out[mine] = my_score;
             const unsigned long long k = best_key(my_score, mine);
             key = k > key ? k : key;
         }
-        __syncwarp();  // the stage is rewritten two iterations from now
+        mut_idx0 = mut_idx1; mut_val0 = mut_val1; any0 = any1;
+        if (it + 2u < iters) dn = sel_begin<ENC>(a, (gwarp + (it + 2u) * nwarps) * 32u + lane);
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     block_best_commit(key, a.best + a.best_slot, warp_best);
 }
 
@@ -947,6 +975,216 @@ __global__ void __launch_bounds__(256) topk_emit(const float* __restrict__ score
             uint32_t g = 0u, e = 0u;
             for (uint32_t w = 0; w < 8u; ++w) { g += w_gt[w]; e += w_eq[w]; }
             run_gt += g; run_eq += e;
+        }
+        __syncthreads();
+    }
+}
+
+// ---- top-k radix select, short form ---------------------------------------------------
+//
+// The same selection in 5 launches instead of 12 (a migration is latency-bound: a
+// dozen dependent 3-us launches cost more than the work inside them).  Three radix
+// passes of 11 + 11 + 10 bits; the last block to finish a pass (ticket counter after
+// a __threadfence) picks the digit, so no separate pick launch; the last block of the
+// count pass scans the per-block counts.  State is left clean for the next call.
+#define TOPK2_BINS 2048u
+struct TopkState2 {
+    uint32_t hist[TOPK2_BINS];
+    uint32_t prefix, mask, remaining;
+    uint32_t threshold, need_eq, total_eq, total_gt;
+    uint32_t ticket;
+};
+
+// block-wide: find the highest bin d with (count of bins above d) + h[d] >= rem.
+// h[] lives in shared memory (nbins <= 2048, 256 threads).  Returns d and the count above it.
+__device__ __forceinline__ void pick_digit(const uint32_t* h, uint32_t nbins, uint32_t rem, uint32_t* out_digit, uint32_t* out_above,
+                                           uint32_t* scratch /* >= 264 words */)
+{
+    const uint32_t t = threadIdx.x, per = nbins / 256u;  // bins per thread, descending order: thread 0 owns the top bins
+    uint32_t mine = 0;
+    for (uint32_t j = 0; j < per; ++j) mine += h[nbins - 1u - (t * per + j)];
+    // inclusive scan of `mine` over threads (warp shuffles + 8 warp totals)
+    uint32_t inc = mine;
+    const uint32_t lane = t & 31u, warp = t >> 5;
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, off);
+        if ((int)lane >= off) inc += o;
+    }
+    if (lane == 31u) scratch[warp] = inc;
+    __syncthreads();
+    uint32_t before_warp = 0;
+    for (uint32_t w2 = 0; w2 < warp; ++w2) before_warp += scratch[w2];
+    inc += before_warp;
+    const uint32_t excl = inc - mine;  // keys in bins owned by lower-numbered threads (= higher bins)
+    if (excl < rem && inc >= rem) {    // the crossing happens inside this thread's bins; exactly one thread
+        uint32_t above = excl;
+        for (uint32_t j = 0; j < per; ++j) {
+            const uint32_t d = nbins - 1u - (t * per + j);
+            if (above + h[d] >= rem) { *out_digit = d; *out_above = above; break; }
+            above += h[d];
+        }
+    }
+    __syncthreads();
+}
+
+template <uint32_t SHIFT, uint32_t BITS>
+__global__ void __launch_bounds__(256) topk2_histogram(const float* __restrict__ score, uint32_t n, int worst, uint32_t k, TopkState2* st)
+{
+    constexpr uint32_t NBINS = 1u << BITS;
+    __shared__ uint32_t h[TOPK2_BINS];
+    __shared__ uint32_t scratch[16];
+    __shared__ uint32_t is_last, s_digit, s_above;
+    for (uint32_t i = threadIdx.x; i < NBINS; i += 256u) h[i] = 0u;
+    __syncthreads();
+    const bool first = SHIFT + BITS == 32u;  // the first pass starts from an empty prefix
+    const uint32_t prefix = first ? 0u : st->prefix, mask = first ? 0u : st->mask;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t span = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t base = (uint64_t)blockIdx.x * blockDim.x; base < n; base += span) {
+        const uint64_t i = base + threadIdx.x;
+        uint32_t key = 0u;
+        bool hit = false;
+        if (i < n) {
+            key = select_key(__ldg(score + i), worst);
+            hit = (key & mask) == prefix;
+        }
+        const uint32_t digit = (key >> SHIFT) & (NBINS - 1u);
+        const uint32_t voters = __ballot_sync(0xFFFFFFFFu, hit);
+        if (hit) {  // one shared-memory atomic per distinct digit in the warp
+            const uint32_t peers = __match_any_sync(voters, digit);
+            if ((peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&h[digit], (uint32_t)__popc(peers));
+        }
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < NBINS; i += 256u)
+        if (h[i]) atomicAdd(&st->hist[i], h[i]);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = atomicAdd(&st->ticket, 1u) == gridDim.x - 1u;
+    __syncthreads();
+    if (!is_last) return;
+    // last block: all histograms have landed; choose the digit of this pass
+    __threadfence();
+    for (uint32_t i = threadIdx.x; i < NBINS; i += 256u) {
+        h[i] = __ldcg(&st->hist[i]);
+        st->hist[i] = 0u;  // clean for the next pass / next call
+    }
+    __syncthreads();
+    const uint32_t rem = first ? k : st->remaining;
+    pick_digit(h, NBINS, rem, &s_digit, &s_above, scratch);
+    if (threadIdx.x == 0) {
+        const uint32_t d = s_digit, above = s_above;
+        st->remaining = rem - above;
+        st->prefix = prefix | (d << SHIFT);
+        st->mask = mask | ((NBINS - 1u) << SHIFT);
+        st->total_gt = (first ? 0u : st->total_gt) + above;
+        if (SHIFT == 0u) {
+            st->threshold = prefix | d;
+            st->need_eq = rem - above;
+            st->total_eq = h[d];
+        }
+        st->ticket = 0u;
+    }
+}
+
+// per-block counts of keys beyond / equal to the threshold; the last block scans them
+__global__ void __launch_bounds__(256) topk2_count_scan(const float* __restrict__ score, uint32_t n, int worst, TopkState2* st,
+                                                        uint32_t* block_gt, uint32_t* block_eq, uint32_t nb)
+{
+    __shared__ uint32_t s_gt, s_eq, is_last;
+    __shared__ uint32_t wsum[2][8];
+    __shared__ uint32_t carry[2];
+    if (threadIdx.x == 0) { s_gt = 0u; s_eq = 0u; }
+    __syncthreads();
+    const uint32_t T = st->threshold;
+    uint32_t gt = 0u, eq = 0u;
+    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
+    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+        if (i < n) {
+            const uint32_t key = select_key(__ldg(score + i), worst);
+            gt += key > T;
+            eq += key == T;
+        }
+    }
+    for (int off = 16; off >= 1; off >>= 1) {
+        gt += __shfl_xor_sync(0xFFFFFFFFu, gt, off);
+        eq += __shfl_xor_sync(0xFFFFFFFFu, eq, off);
+    }
+    if ((threadIdx.x & 31u) == 0u) { atomicAdd(&s_gt, gt); atomicAdd(&s_eq, eq); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        block_gt[blockIdx.x] = s_gt;
+        block_eq[blockIdx.x] = s_eq;
+        __threadfence();
+        is_last = atomicAdd(&st->ticket, 1u) == gridDim.x - 1u;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    // exclusive scan of both arrays in place, 256 entries at a time
+    const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
+    if (t == 0) { carry[0] = 0u; carry[1] = 0u; st->ticket = 0u; }
+    __syncthreads();
+    for (uint32_t b0 = 0; b0 < nb; b0 += 256u) {
+        const uint32_t i = b0 + t;
+        uint32_t v[2] = { i < nb ? __ldcg(block_gt + i) : 0u, i < nb ? __ldcg(block_eq + i) : 0u };
+        uint32_t inc[2] = { v[0], v[1] };
+        for (int q = 0; q < 2; ++q) {
+            for (int off = 1; off < 32; off <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc[q], off);
+                if ((int)lane >= off) inc[q] += o;
+            }
+            if (lane == 31u) wsum[q][warp] = inc[q];
+        }
+        __syncthreads();
+        uint32_t tot[2];
+        for (int q = 0; q < 2; ++q) {
+            uint32_t before = carry[q];
+            for (uint32_t w2 = 0; w2 < warp; ++w2) before += wsum[q][w2];
+            const uint32_t excl = before + inc[q] - v[q];
+            if (i < nb) (q == 0 ? block_gt : block_eq)[i] = excl;
+            tot[q] = excl + v[q];
+        }
+        __syncthreads();
+        if (t == 255u) { carry[0] = tot[0]; carry[1] = tot[1]; }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) topk2_emit(const float* __restrict__ score, uint32_t n, int worst, const TopkState2* st,
+                                                  const uint32_t* block_gt, const uint32_t* block_eq, uint32_t* out_idx)
+{
+    __shared__ uint32_t w_gt[8], w_eq[8];
+    __shared__ uint32_t run_gt, run_eq;
+    const uint32_t T = st->threshold, need = st->need_eq, total_eq = st->total_eq;
+    const uint32_t eq_lo = worst ? total_eq - need : 0u, eq_hi = worst ? total_eq : need;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { run_gt = block_gt[blockIdx.x]; run_eq = block_eq[blockIdx.x]; }
+    __syncthreads();
+    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
+    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+        bool gt = false, eq = false;
+        if (i < n) {
+            const uint32_t key = select_key(__ldg(score + i), worst);
+            gt = key > T;
+            eq = key == T;
+        }
+        const uint32_t bg = __ballot_sync(0xFFFFFFFFu, gt), be = __ballot_sync(0xFFFFFFFFu, eq);
+        const uint32_t lt_mask = (1u << lane) - 1u;
+        if (lane == 0) { w_gt[warp] = __popc(bg); w_eq[warp] = __popc(be); }
+        __syncthreads();
+        uint32_t gt_before = run_gt + __popc(bg & lt_mask), eq_before = run_eq + __popc(be & lt_mask);
+        for (uint32_t w2 = 0; w2 < warp; ++w2) { gt_before += w_gt[w2]; eq_before += w_eq[w2]; }
+        const uint32_t eq_sel_before = eq_before <= eq_lo ? 0u : (eq_before >= eq_hi ? eq_hi - eq_lo : eq_before - eq_lo);
+        if (gt) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
+        else if (eq && eq_before >= eq_lo && eq_before < eq_hi) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t g2 = 0u, e2 = 0u;
+            for (uint32_t w2 = 0; w2 < 8u; ++w2) { g2 += w_gt[w2]; e2 += w_eq[w2]; }
+            run_gt += g2; run_eq += e2;
         }
         __syncthreads();
     }
