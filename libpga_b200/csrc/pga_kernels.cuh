@@ -80,10 +80,14 @@ __device__ __forceinline__ void block_best_commit(unsigned long long key, unsign
 // ---- hook path ----------------------------------------------------------------
 //
 // Block of T threads <-> T consecutive children.  Shared memory holds, per thread,
-// the child row and (crossover phase) both parent rows, plus the rand row when a
-// hook wants one.  Parent rows arrive by one TMA bulk copy each, issued by the
-// thread that ran the tournament; the block's child rows leave by ONE bulk store,
-// because consecutive children are contiguous in next_gen.
+// the child row, plus the rand row when a hook wants one, plus -- when the user
+// supplied a crossover hook, which must be handed two contiguous parent rows -- both
+// parents.  Those parent rows arrive by one TMA bulk copy each, issued by the thread
+// that ran the tournament.  With the default crossover the parents are never staged:
+// each warp reads them straight from global memory with coalesced 128-bit loads while
+// it builds its 32 children, which leaves four times as many threads resident.  The
+// block's child rows leave by ONE bulk store, because consecutive children are
+// contiguous in next_gen.
 template <uint32_t PH>
 __global__ void __launch_bounds__(128) generation_hooks(const __grid_constant__ GenArgs a)
 {
@@ -96,10 +100,11 @@ __global__ void __launch_bounds__(128) generation_hooks(const __grid_constant__ 
     const uint32_t S = a.stride;
     const bool want_rand = ((PH & PH_CROSSOVER) && a.xov != nullptr) || ((PH & PH_MUTATE) && a.mut != nullptr);
 
+    const bool stage_parents = (PH & PH_CROSSOVER) && a.xov != nullptr;
     float* s_child = rows;
     float* s_p1 = s_child + (size_t)T * S;
-    float* s_p2 = (PH & PH_CROSSOVER) ? s_p1 + (size_t)T * S : s_p1;
-    float* s_rnd = (PH & PH_CROSSOVER) ? s_p2 + (size_t)T * S : s_p1;
+    float* s_p2 = stage_parents ? s_p1 + (size_t)T * S : s_p1;
+    float* s_rnd = stage_parents ? s_p2 + (size_t)T * S : s_p1;
 
     const uint32_t base = blockIdx.x * T;
     const uint32_t nact = min(T, a.n - base);
@@ -120,14 +125,17 @@ __global__ void __launch_bounds__(128) generation_hooks(const __grid_constant__ 
         u0 = to_uniform(w.x); u1 = to_uniform(w.y); u2 = to_uniform(w.z); u3 = to_uniform(w.w);
     }
 
+    uint32_t p1 = 0, p2 = 0;
     if (PH & PH_CROSSOVER) {
-        if (t == 0) mbar_arrive_expect_tx(bar, nact * 2u * row_bytes);
+        if (stage_parents && t == 0) mbar_arrive_expect_tx(bar, nact * 2u * row_bytes);
         if (active) {
-            const uint32_t p1 = tournament(a.score_in, u0, u1, a.nf, a.n);  // src/pga.cu:306
-            const uint32_t p2 = tournament(a.score_in, u2, u3, a.nf, a.n);  // src/pga.cu:307
+            p1 = tournament(a.score_in, u0, u1, a.nf, a.n);  // src/pga.cu:306
+            p2 = tournament(a.score_in, u2, u3, a.nf, a.n);  // src/pga.cu:307
             if (a.sel) { a.sel[2 * (size_t)i] = (int32_t)p1; a.sel[2 * (size_t)i + 1] = (int32_t)p2; }
-            bulk_load(s_p1 + (size_t)t * S, a.cur + (size_t)p1 * S, row_bytes, bar);
-            bulk_load(s_p2 + (size_t)t * S, a.cur + (size_t)p2 * S, row_bytes, bar);
+            if (stage_parents) {
+                bulk_load(s_p1 + (size_t)t * S, a.cur + (size_t)p1 * S, row_bytes, bar);
+                bulk_load(s_p2 + (size_t)t * S, a.cur + (size_t)p2 * S, row_bytes, bar);
+            }
         }
     } else {
         // the block's own rows are contiguous: one copy
@@ -152,7 +160,7 @@ __global__ void __launch_bounds__(128) generation_hooks(const __grid_constant__ 
         }
     }
 
-    mbar_wait(bar, 0);
+    if (!(PH & PH_CROSSOVER) || stage_parents) mbar_wait(bar, 0);
     __syncwarp();
 
     if (PH & PH_CROSSOVER) {
@@ -163,26 +171,46 @@ __global__ void __launch_bounds__(128) generation_hooks(const __grid_constant__ 
                 for (uint32_t j = a.len; j < S; ++j) c[j] = 0.f;
             }
         } else {
-            // default uniform crossover (src/pga.cu:135-143), cooperative per warp
-            for (uint32_t c = 0; c < 32u; ++c) {
-                const uint32_t tt = warp * 32u + c;
-                if (tt >= nact) break;
-                for (uint32_t b = lane; b < (S >> 2); b += 32u) {
-                    float4 r;
-                    if (want_rand) {
-                        r = *reinterpret_cast<const float4*>(s_rnd + (size_t)tt * S + 4u * b);
-                    } else {
-                        const uint4 w = draw_block(a.draw, STREAM_ROW, base + tt, b);
-                        r = make_float4(to_uniform(w.x), to_uniform(w.y), to_uniform(w.z), to_uniform(w.w));
+            // default uniform crossover (src/pga.cu:135-143), cooperative per warp: four
+            // children at a time, lanes across 16-byte blocks, parents read from global
+            const uint4* __restrict__ cur4 = reinterpret_cast<const uint4*>(a.cur);
+            const uint32_t nblk = S >> 2;
+            for (uint32_t c0 = 0; c0 < 32u; c0 += 4u) {
+                if (warp * 32u + c0 >= nact) break;  // warp-uniform
+                uint32_t q1[4], q2[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    q1[u] = __shfl_sync(0xFFFFFFFFu, p1, c0 + u);
+                    q2[u] = __shfl_sync(0xFFFFFFFFu, p2, c0 + u);
+                }
+                for (uint32_t b = lane; b < nblk; b += 32u) {
+                    uint4 x[4], y[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        x[u] = load_row_block(cur4 + (size_t)q1[u] * nblk + b);
+                        y[u] = load_row_block(cur4 + (size_t)q2[u] * nblk + b);
                     }
-                    const float4 x = *reinterpret_cast<const float4*>(s_p1 + (size_t)tt * S + 4u * b);
-                    const float4 y = *reinterpret_cast<const float4*>(s_p2 + (size_t)tt * S + 4u * b);
-                    float4 o;
-                    o.x = r.x > 0.5f ? x.x : y.x;
-                    o.y = r.y > 0.5f ? x.y : y.y;
-                    o.z = r.z > 0.5f ? x.z : y.z;
-                    o.w = r.w > 0.5f ? x.w : y.w;
-                    *reinterpret_cast<float4*>(s_child + (size_t)tt * S + 4u * b) = o;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const uint32_t tt = warp * 32u + c0 + u;
+                        if (tt < nact) {
+                            uint4 w;
+                            if (want_rand) {
+                                const float4 r = *reinterpret_cast<const float4*>(s_rnd + (size_t)tt * S + 4u * b);
+                                // the rand row holds the uniforms themselves: compare as floats
+                                w.x = r.x > 0.5f ? 0xFFFFFFFFu : 0u; w.y = r.y > 0.5f ? 0xFFFFFFFFu : 0u;
+                                w.z = r.z > 0.5f ? 0xFFFFFFFFu : 0u; w.w = r.w > 0.5f ? 0xFFFFFFFFu : 0u;
+                            } else {
+                                w = draw_block(a.draw, STREAM_ROW, base + tt, b);
+                            }
+                            uint4 o;
+                            o.x = draw_above_half(w.x) ? x[u].x : y[u].x;
+                            o.y = draw_above_half(w.y) ? x[u].y : y[u].y;
+                            o.z = draw_above_half(w.z) ? x[u].z : y[u].z;
+                            o.w = draw_above_half(w.w) ? x[u].w : y[u].w;
+                            *reinterpret_cast<uint4*>(s_child + (size_t)tt * S + 4u * b) = o;
+                        }
+                    }
                 }
             }
         }
