@@ -146,7 +146,7 @@ def configure(pg, g, w):
         g.tsp_load(np.array(tok[1:1 + n * n], dtype=np.float32).reshape(n, n))
 
 
-def run_reference_arm(args, w):
+def run_reference_arm(args, w, emit):
     """The CPU oracle on all host cores: a bounded sample of the same workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -192,7 +192,7 @@ def run_reference_arm(args, w):
         "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def cpu_baseline(w):
@@ -223,6 +223,14 @@ def cpu_baseline(w):
 
 
 def main():
+    # the contract is ONE JSON line on stdout: libraries (NCCL prints its version banner
+    # to stdout) must not get there, so fd 1 points at stderr until the line is ready
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
+
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -243,7 +251,7 @@ def main():
         w["label"] += f" (size overridden to {args.size})"
 
     if args.impl == "reference":
-        run_reference_arm(args, w)
+        run_reference_arm(args, w, emit)
         return
 
     import numpy as np
@@ -365,7 +373,7 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
 
 
 if __name__ == "__main__":

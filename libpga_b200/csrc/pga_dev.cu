@@ -49,6 +49,8 @@ struct pgadev_ctx {
     int fast_blocks_per_sm_set;
     int force_generic;            // $PGA_FORCE_GENERIC=1: skip the compile-time tiled kernels
     int staged;                   // $PGA_STAGED=1: small rows take the cp.async-staged kernel instead
+    int no_coop;                  // $PGA_NO_COOP=1: rank with the 5-launch select instead of the cooperative kernel
+    uint32_t reserve_now;         // SMs' worth of blocks the current launch leaves free (pgadev_step.reserve_sms)
 };
 
 struct pgadev_pop {
@@ -67,6 +69,8 @@ struct pgadev_pop {
     int capture;
     // ranking scratch
     TopkState2* topk[2];  // one set per index list: emigrants may be ranked on the side stream
+    TopkCoop* coop[2];
+    unsigned long long coop_arrivals[2];  // barrier arrivals consumed so far by the cooperative select
     uint32_t *blk_gt[2], *blk_eq[2];
     uint32_t nb;
     uint32_t* idx[2];
@@ -100,8 +104,12 @@ extern "C" pgadev_ctx* pgadev_ctx_create(void)
     cudaDeviceProp prop;
     CCE(cudaGetDeviceProperties(&prop, c->device));
     c->sm_count = prop.multiProcessorCount;
-    CCE(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
-    CCE(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    // the side stream (emigrant ranking, packing, NCCL) gets the highest priority so its
+    // small kernels are placed ahead of the next generation's blocks
+    int prio_lo = 0, prio_hi = 0;
+    CCE(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CCE(cudaStreamCreateWithPriority(&c->own_stream, cudaStreamNonBlocking, prio_lo));
+    CCE(cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, prio_hi));
     c->stream = c->own_stream;
     CCE(cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming));
     CCE(cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming));
@@ -115,6 +123,7 @@ extern "C" pgadev_ctx* pgadev_ctx_create(void)
     c->fast_blocks_per_sm_set = e && atoi(e) > 0;
     c->force_generic = (e = getenv("PGA_FORCE_GENERIC")) ? atoi(e) : 0;
     c->staged = (e = getenv("PGA_STAGED")) ? atoi(e) : 0;
+    c->no_coop = (e = getenv("PGA_NO_COOP")) ? atoi(e) : 0;
     const char* stack = getenv("PGA_STACK_BYTES");  // device stack for deep user hooks
     if (stack && atoi(stack) > 0) CCE(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(stack)));
     return c;
@@ -199,6 +208,7 @@ extern "C" void pgadev_pop_destroy(pgadev_ctx* c, pgadev_pop* p)
     if (p->sel) CCE(cudaFree(p->sel));
     for (int i = 0; i < 2; ++i) {
         if (p->topk[i]) CCE(cudaFree(p->topk[i]));
+        if (p->coop[i]) CCE(cudaFree(p->coop[i]));
         if (p->blk_gt[i]) CCE(cudaFree(p->blk_gt[i]));
         if (p->blk_eq[i]) CCE(cudaFree(p->blk_eq[i]));
     }
@@ -302,9 +312,11 @@ static int launch_tiled_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
         if (blocks_per_sm < 1) blocks_per_sm = 1;
         configured_for = c->device;
     }
-    // exactly one resident wave (a partial second wave costs a full kernel tail)
+    // exactly one resident wave (a partial second wave costs a full kernel tail), minus
+    // the blocks held back so that side-stream work can run beside this launch
     const uint32_t per_sm = c->fast_blocks_per_sm_set ? c->fast_blocks_per_sm : (uint32_t)blocks_per_sm;
-    const uint32_t grid = grid_for(p->n, 256, (uint32_t)c->sm_count * per_sm);
+    const uint32_t sms = (uint32_t)c->sm_count - (c->reserve_now < (uint32_t)c->sm_count / 2u ? c->reserve_now : (uint32_t)c->sm_count / 2u);
+    const uint32_t grid = grid_for(p->n, 256, sms * per_sm);
     generation_fused_tiled<ENC, OBJ, LOGG, NB, TB, EXACT, MINB><<<grid, 256, 0, c->stream>>>(a);
     LAUNCH_CHECK(c);
     return 0;
@@ -420,6 +432,7 @@ extern "C" int pgadev_launch(pgadev_ctx* c, pgadev_pop* p, const pgadev_step* st
     const uint32_t ph = st->phases;
     if (ph != PH_FUSED && ph != PH_EVALUATE && ph != PH_CROSSOVER && ph != PH_MUTATE) return PGAX_EINVAL;
 
+    c->reserve_now = st->reserve_sms;
     GenArgs a;
     memset(&a, 0, sizeof(a));
     a.cur = p->genes[p->gidx];
@@ -577,6 +590,45 @@ static void ensure_index_list(pgadev_ctx* c, pgadev_pop* p, int slot, uint64_t k
 
 static cudaStream_t work_stream(pgadev_ctx* c) { return c->route_side ? c->side : c->stream; }
 
+// The whole selection as one cooperative launch, when the population is small enough
+// for every block to be resident at once (E scores per thread, E = 8, 16 or 32).
+template <int E>
+static bool select_top_coop_e(pgadev_ctx* c, pgadev_pop* p, uint32_t k, int worst, int slot, cudaStream_t s)
+{
+    static int configured_for = -1;
+    static int blocks_per_sm = 0;
+    if (configured_for != c->device) {
+        CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, topk_select_coop<E>, 256, 0));
+        configured_for = c->device;
+    }
+    const uint64_t per_block = 256ull * E;
+    const uint64_t grid = (p->n + per_block - 1) / per_block;
+    if (grid > (uint64_t)blocks_per_sm * (uint64_t)c->sm_count) return false;
+    if (!p->coop[slot]) {
+        CCE(cudaMalloc((void**)&p->coop[slot], sizeof(TopkCoop)));
+        CCE(cudaMemset(p->coop[slot], 0, sizeof(TopkCoop)));
+        p->coop_arrivals[slot] = 0;
+    }
+    const float* score = p->score[p->sidx];
+    uint32_t n = (uint32_t)p->n;
+    TopkCoop* st = p->coop[slot];
+    uint32_t *bg = p->blk_gt[slot], *be = p->blk_eq[slot], *out = p->idx[slot];
+    unsigned long long base = p->coop_arrivals[slot];
+    void* args[] = { (void*)&score, (void*)&n, (void*)&k, (void*)&worst, (void*)&st, (void*)&bg, (void*)&be, (void*)&out, (void*)&base };
+    CCE(cudaLaunchCooperativeKernel((const void*)topk_select_coop<E>, dim3((unsigned)grid), dim3(256), args, 0, s));
+    c->launches += 1;
+    p->coop_arrivals[slot] += 4ull * grid;  // four grid barriers per call
+    return true;
+}
+
+static bool select_top_coop(pgadev_ctx* c, pgadev_pop* p, uint32_t k, int worst, int slot, cudaStream_t s)
+{
+    if (c->no_coop) return false;
+    if (select_top_coop_e<8>(c, p, k, worst, slot, s)) return true;
+    if (select_top_coop_e<16>(c, p, k, worst, slot, s)) return true;
+    return select_top_coop_e<32>(c, p, k, worst, slot, s);
+}
+
 extern "C" void pgadev_route_to_side(pgadev_ctx* c, int on) { c->route_side = on; }
 
 extern "C" void pgadev_select_top(pgadev_ctx* c, pgadev_pop* p, uint64_t k, int worst, int slot)
@@ -596,9 +648,10 @@ extern "C" void pgadev_select_top(pgadev_ctx* c, pgadev_pop* p, uint64_t k, int 
     uint32_t *bg = p->blk_gt[slot], *be = p->blk_eq[slot];
     const float* score = p->score[p->sidx];
     const uint32_t n = (uint32_t)p->n;
+    if (select_top_coop(c, p, (uint32_t)k, worst, slot, s)) return;
     // five launches: three radix passes (the last block of each picks the digit), the
     // per-block counts (the last block scans them), the stable compaction
-    const uint32_t hgrid = grid_for(p->n, 256 * 4, (uint32_t)c->sm_count * 4u);
+    const uint32_t hgrid = p->nb;  // one 2048-score chunk per block
     topk2_histogram<21, 11><<<hgrid, 256, 0, s>>>(score, n, worst, (uint32_t)k, st);
     LAUNCH_CHECK(c);
     topk2_histogram<10, 11><<<hgrid, 256, 0, s>>>(score, n, worst, (uint32_t)k, st);

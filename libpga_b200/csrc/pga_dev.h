@@ -37,6 +37,7 @@ typedef struct pgadev_step {
 	void *obj_hook;  /* device code addresses, NULL = default / built-in */
 	void *mutate_hook;
 	void *crossover_hook;
+	uint32_t reserve_sms; /* leave this many SMs' worth of blocks unlaunched, for work on the side stream */
 } pgadev_step;
 
 pgadev_ctx *pgadev_ctx_create(void);

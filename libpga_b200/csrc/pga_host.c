@@ -45,6 +45,8 @@ struct pga { /* reference: src/pga.cu:48-56 */
 	uint32_t migrate_round;
 	int rank, world; /* island layout across processes */
 	int have_comm;
+	unsigned reserve_sms;   /* blocks held back in the next launches (an exchange is in flight beside them) */
+	unsigned reserve_conf;  /* $PGA_RESERVE_SMS, default 8 */
 	float last_run_ms;
 	pgadev_ctx *dev;
 };
@@ -70,6 +72,8 @@ pga_t *pga_init() /* src/pga.cu:148-164 */
 	p->builtin = PGAX_OBJ_HOOK;
 	p->topology = PGAX_TOPO_RANDOM; /* "random migrations", include/pga.h:148 */
 	p->delay = 1;
+	env = getenv("PGA_RESERVE_SMS");
+	p->reserve_conf = env && *env ? (unsigned)strtoul(env, NULL, 0) : 8u;
 	p->rank = 0;
 	p->world = 1;
 	p->dev = pgadev_ctx_create();
@@ -158,6 +162,7 @@ static void fill_step(pga_t *p, population_t *pop, unsigned phases, pgadev_step 
 	st->obj_hook = (void *)p->objective;
 	st->mutate_hook = (void *)p->mutate;
 	st->crossover_hook = (void *)p->crossover;
+	st->reserve_sms = p->reserve_sms;
 	if ((phases & PGADEV_PH_EVALUATE) && p->builtin == PGAX_OBJ_HOOK && p->objective == NULL)
 		die("no objective function set (pga_set_objective_function)");
 }
@@ -652,8 +657,12 @@ void pga_run_islands(pga_t *p, unsigned n, unsigned m, float pct) /* stub: src/p
 		/* generation start+2 overwrites the buffers the emigrants are packed from */
 		if (ex.active && g == ex.start_gen + 2)
 			pgadev_main_wait_packed(p->dev);
+		/* while an exchange is being ranked, packed and sent on the side stream the
+		 * generation kernel leaves a few SMs free for it */
+		p->reserve_sms = ex.active ? p->reserve_conf : 0;
 		for (unsigned s = 0; s < p->p_count; ++s)
 			generation_async(p, p->populations[s]);
+		p->reserve_sms = 0;
 		if (ex.active && ex.land_gen == g)
 			exchange_finish(p, &ex);
 		if (m && g % m == 0 && g + p->delay <= n && total > 1 && !ex.active) {

@@ -1062,20 +1062,25 @@ __global__ void __launch_bounds__(256) topk2_histogram(const float* __restrict__
     __shared__ uint32_t h[TOPK2_BINS];
     __shared__ uint32_t scratch[16];
     __shared__ uint32_t is_last, s_digit, s_above;
+    // one 2048-score chunk per block; all eight loads of a thread are issued before the
+    // first is used (the ballots below would otherwise serialise eight round trips)
+    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
+    float v[TOPK_ROUNDS];
+#pragma unroll
+    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+        v[r] = i < n ? __ldg(score + i) : 0.f;
+    }
     for (uint32_t i = threadIdx.x; i < NBINS; i += 256u) h[i] = 0u;
     __syncthreads();
     const bool first = SHIFT + BITS == 32u;  // the first pass starts from an empty prefix
     const uint32_t prefix = first ? 0u : st->prefix, mask = first ? 0u : st->mask;
     const uint32_t lane = threadIdx.x & 31u;
-    const uint64_t span = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t base = (uint64_t)blockIdx.x * blockDim.x; base < n; base += span) {
-        const uint64_t i = base + threadIdx.x;
-        uint32_t key = 0u;
-        bool hit = false;
-        if (i < n) {
-            key = select_key(__ldg(score + i), worst);
-            hit = (key & mask) == prefix;
-        }
+#pragma unroll
+    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+        const uint32_t key = select_key(v[r], worst);
+        const bool hit = i < n && (key & mask) == prefix;
         const uint32_t digit = (key >> SHIFT) & (NBINS - 1u);
         const uint32_t voters = __ballot_sync(0xFFFFFFFFu, hit);
         if (hit) {  // one shared-memory atomic per distinct digit in the warp
@@ -1124,16 +1129,21 @@ __global__ void __launch_bounds__(256) topk2_count_scan(const float* __restrict_
     __shared__ uint32_t carry[2];
     if (threadIdx.x == 0) { s_gt = 0u; s_eq = 0u; }
     __syncthreads();
-    const uint32_t T = st->threshold;
-    uint32_t gt = 0u, eq = 0u;
     const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
+    float v[TOPK_ROUNDS];
+#pragma unroll
     for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
         const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
-        if (i < n) {
-            const uint32_t key = select_key(__ldg(score + i), worst);
-            gt += key > T;
-            eq += key == T;
-        }
+        v[r] = i < n ? __ldg(score + i) : 0.f;
+    }
+    const uint32_t T = st->threshold;
+    uint32_t gt = 0u, eq = 0u;
+#pragma unroll
+    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+        const uint32_t key = select_key(v[r], worst);
+        gt += i < n && key > T;
+        eq += i < n && key == T;
     }
     for (int off = 16; off >= 1; off >>= 1) {
         gt += __shfl_xor_sync(0xFFFFFFFFu, gt, off);
@@ -1183,38 +1193,181 @@ __global__ void __launch_bounds__(256) topk2_count_scan(const float* __restrict_
 __global__ void __launch_bounds__(256) topk2_emit(const float* __restrict__ score, uint32_t n, int worst, const TopkState2* st,
                                                   const uint32_t* block_gt, const uint32_t* block_eq, uint32_t* out_idx)
 {
+    // Each warp owns 256 CONSECUTIVE scores of the block's chunk (8 sub-rounds of 32), so
+    // index order is warp-major and the block needs one barrier: warp totals -> prefix.
     __shared__ uint32_t w_gt[8], w_eq[8];
-    __shared__ uint32_t run_gt, run_eq;
     const uint32_t T = st->threshold, need = st->need_eq, total_eq = st->total_eq;
+    // "best": the first `need` equal keys by index; "worst": the last `need`
     const uint32_t eq_lo = worst ? total_eq - need : 0u, eq_hi = worst ? total_eq : need;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) { run_gt = block_gt[blockIdx.x]; run_eq = block_eq[blockIdx.x]; }
-    __syncthreads();
-    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
+    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK + warp * 256u;
+    float v[TOPK_ROUNDS];
+#pragma unroll
     for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
-        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
-        bool gt = false, eq = false;
-        if (i < n) {
-            const uint32_t key = select_key(__ldg(score + i), worst);
-            gt = key > T;
-            eq = key == T;
-        }
-        const uint32_t bg = __ballot_sync(0xFFFFFFFFu, gt), be = __ballot_sync(0xFFFFFFFFu, eq);
-        const uint32_t lt_mask = (1u << lane) - 1u;
-        if (lane == 0) { w_gt[warp] = __popc(bg); w_eq[warp] = __popc(be); }
-        __syncthreads();
-        uint32_t gt_before = run_gt + __popc(bg & lt_mask), eq_before = run_eq + __popc(be & lt_mask);
-        for (uint32_t w2 = 0; w2 < warp; ++w2) { gt_before += w_gt[w2]; eq_before += w_eq[w2]; }
+        const uint64_t i = base + r * 32u + lane;
+        v[r] = i < n ? __ldg(score + i) : 0.f;
+    }
+    uint32_t bg[TOPK_ROUNDS], be[TOPK_ROUNDS], tot_g = 0u, tot_e = 0u;
+#pragma unroll
+    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+        const uint64_t i = base + r * 32u + lane;
+        const uint32_t key = select_key(v[r], worst);
+        bg[r] = __ballot_sync(0xFFFFFFFFu, i < n && key > T);
+        be[r] = __ballot_sync(0xFFFFFFFFu, i < n && key == T);
+        tot_g += __popc(bg[r]);
+        tot_e += __popc(be[r]);
+    }
+    if (lane == 0) { w_gt[warp] = tot_g; w_eq[warp] = tot_e; }
+    __syncthreads();
+    uint32_t run_g = block_gt[blockIdx.x], run_e = block_eq[blockIdx.x];
+    for (uint32_t w2 = 0; w2 < warp; ++w2) { run_g += w_gt[w2]; run_e += w_eq[w2]; }
+    const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+        const uint64_t i = base + r * 32u + lane;
+        const bool gt = (bg[r] >> lane) & 1u, eq = (be[r] >> lane) & 1u;
+        const uint32_t gt_before = run_g + __popc(bg[r] & lt_mask), eq_before = run_e + __popc(be[r] & lt_mask);
+        // position among the selected = selected elements with a lower index
         const uint32_t eq_sel_before = eq_before <= eq_lo ? 0u : (eq_before >= eq_hi ? eq_hi - eq_lo : eq_before - eq_lo);
         if (gt) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
         else if (eq && eq_before >= eq_lo && eq_before < eq_hi) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
+        run_g += __popc(bg[r]);
+        run_e += __popc(be[r]);
+    }
+}
+
+// ---- top-k select in ONE cooperative launch ------------------------------------------
+//
+// A migration is latency-bound: the 5-launch select above spends ~7 us per launch on
+// launch gaps, a fresh round trip to the scores and the last-block hand-over.  Here the
+// whole selection is one kernel whose blocks are all resident (cooperative launch):
+// every thread loads its E scores ONCE and keeps the keys in registers through the
+// three radix passes, the count and the compaction; the phases are separated by four
+// grid barriers.  Every block derives the chosen digit itself from the global
+// histogram, so no block has to publish a decision.
+struct TopkCoop {
+    uint32_t hist[3][TOPK2_BINS];  // one histogram per pass; zeroed again before the kernel ends
+    unsigned long long arrive;     // monotonic barrier counter (never reset)
+};
+
+__device__ __forceinline__ void grid_barrier(unsigned long long* ctr, unsigned long long target)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(ctr, 1ull);
+        while (*reinterpret_cast<volatile unsigned long long*>(ctr) < target) { }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+template <int E>
+__global__ void __launch_bounds__(256, E == 8 ? 4 : (E == 16 ? 3 : 2)) topk_select_coop(const float* __restrict__ score, uint32_t n, uint32_t k, int worst,
+                                                        TopkCoop* st, uint32_t* blk_gt, uint32_t* blk_eq, uint32_t* out_idx,
+                                                        unsigned long long barrier_base)
+{
+    __shared__ uint32_t h[TOPK2_BINS];
+    __shared__ uint32_t scratch[16];
+    __shared__ uint32_t s_digit, s_above;
+    __shared__ uint32_t w_gt[8], w_eq[8];
+    __shared__ uint32_t s_before[2];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    // warp-major layout: each warp owns 32*E consecutive scores, so index order is
+    // (block, warp, round, lane) and the compaction needs no block-wide scan per round
+    const uint64_t base = ((uint64_t)blockIdx.x * 8u + warp) * (32u * E);
+    uint32_t key[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const uint64_t i = base + (uint32_t)r * 32u + lane;
+        key[r] = i < n ? select_key(__ldg(score + i), worst) : 0u;
+    }
+    const uint64_t last_valid = n;  // elements at or past n never vote
+
+    uint32_t prefix = 0u, mask = 0u, rem = k, total_eq = 0u;
+#pragma unroll
+    for (int pass = 0; pass < 3; ++pass) {
+        const uint32_t shift = pass == 0 ? 21u : (pass == 1 ? 10u : 0u);
+        const uint32_t nbins = pass == 2 ? 1024u : 2048u;
+        for (uint32_t i = threadIdx.x; i < nbins; i += 256u) h[i] = 0u;
         __syncthreads();
-        if (threadIdx.x == 0) {
-            uint32_t g2 = 0u, e2 = 0u;
-            for (uint32_t w2 = 0; w2 < 8u; ++w2) { g2 += w_gt[w2]; e2 += w_eq[w2]; }
-            run_gt += g2; run_eq += e2;
+#pragma unroll
+        for (int r = 0; r < E; ++r) {
+            const uint64_t i = base + (uint32_t)r * 32u + lane;
+            const bool hit = i < last_valid && (key[r] & mask) == prefix;
+            const uint32_t digit = (key[r] >> shift) & (nbins - 1u);
+            const uint32_t voters = __ballot_sync(0xFFFFFFFFu, hit);
+            if (hit) {
+                const uint32_t peers = __match_any_sync(voters, digit);
+                if ((peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&h[digit], (uint32_t)__popc(peers));
+            }
         }
         __syncthreads();
+        for (uint32_t i = threadIdx.x; i < nbins; i += 256u)
+            if (h[i]) atomicAdd(&st->hist[pass][i], h[i]);
+        grid_barrier(&st->arrive, barrier_base + (unsigned long long)(pass + 1) * gridDim.x);
+        for (uint32_t i = threadIdx.x; i < nbins; i += 256u) h[i] = __ldcg(&st->hist[pass][i]);
+        __syncthreads();
+        pick_digit(h, nbins, rem, &s_digit, &s_above, scratch);
+        const uint32_t d = s_digit, above = s_above;
+        if (pass == 2) total_eq = h[d];
+        prefix |= d << shift;
+        mask |= (nbins - 1u) << shift;
+        rem -= above;
+        __syncthreads();
+    }
+    const uint32_t T = prefix, need = rem;
+
+    // counts of keys beyond / equal to the threshold, per warp and per block
+    uint32_t tot_g = 0u, tot_e = 0u;
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const uint64_t i = base + (uint32_t)r * 32u + lane;
+        tot_g += __popc(__ballot_sync(0xFFFFFFFFu, i < last_valid && key[r] > T));
+        tot_e += __popc(__ballot_sync(0xFFFFFFFFu, i < last_valid && key[r] == T));
+    }
+    if (lane == 0) { w_gt[warp] = tot_g; w_eq[warp] = tot_e; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t g2 = 0u, e2 = 0u;
+        for (uint32_t w2 = 0; w2 < 8u; ++w2) { g2 += w_gt[w2]; e2 += w_eq[w2]; }
+        blk_gt[blockIdx.x] = g2;
+        blk_eq[blockIdx.x] = e2;
+    }
+    grid_barrier(&st->arrive, barrier_base + 4ull * gridDim.x);
+
+    // the histograms are no longer read by anyone: clean them for the next call
+    if (blockIdx.x == 0)
+        for (uint32_t i = threadIdx.x; i < 3u * TOPK2_BINS; i += 256u) (&st->hist[0][0])[i] = 0u;
+
+    // selected elements in the blocks before this one
+    uint32_t bg = 0u, be = 0u;
+    for (uint32_t b2 = threadIdx.x; b2 < blockIdx.x; b2 += 256u) { bg += __ldcg(blk_gt + b2); be += __ldcg(blk_eq + b2); }
+    for (int off = 16; off >= 1; off >>= 1) {
+        bg += __shfl_xor_sync(0xFFFFFFFFu, bg, off);
+        be += __shfl_xor_sync(0xFFFFFFFFu, be, off);
+    }
+    if (threadIdx.x == 0) { s_before[0] = 0u; s_before[1] = 0u; }
+    __syncthreads();
+    if (lane == 0) { atomicAdd(&s_before[0], bg); atomicAdd(&s_before[1], be); }
+    __syncthreads();
+    uint32_t run_g = s_before[0], run_e = s_before[1];
+    for (uint32_t w2 = 0; w2 < warp; ++w2) { run_g += w_gt[w2]; run_e += w_eq[w2]; }
+
+    // "best": the first `need` equal keys by index; "worst": the last `need`
+    const uint32_t eq_lo = worst ? total_eq - need : 0u, eq_hi = worst ? total_eq : need;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const uint64_t i = base + (uint32_t)r * 32u + lane;
+        const bool gt = i < last_valid && key[r] > T, eq = i < last_valid && key[r] == T;
+        const uint32_t mg = __ballot_sync(0xFFFFFFFFu, gt), me = __ballot_sync(0xFFFFFFFFu, eq);
+        const uint32_t gt_before = run_g + __popc(mg & lt_mask), eq_before = run_e + __popc(me & lt_mask);
+        const uint32_t eq_sel_before = eq_before <= eq_lo ? 0u : (eq_before >= eq_hi ? eq_hi - eq_lo : eq_before - eq_lo);
+        if (gt) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
+        else if (eq && eq_before >= eq_lo && eq_before < eq_hi) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
+        run_g += __popc(mg);
+        run_e += __popc(me);
     }
 }
 
