@@ -41,7 +41,7 @@ WORKLOADS = {
 
 
 KERNELS = {
-    "onemax": "generation_fused_tiled<ENC_BITS, OBJ_ONEMAX, LOGG=2, NB=2, TB=4>",
+    "onemax": "generation_fused_tiled<ENC_BITS, OBJ_ONEMAX, LOGG=3, NB=1, TB=8>",
     "rastrigin": "generation_fused_tiled<ENC_F32, OBJ_RASTRIGIN, LOGG=5, NB=2, TB=2>",
     "test1": "generation_hooks<PH_FUSED> (user objective through a device function pointer)",
     "tsp": "generation_hooks<PH_FUSED> (user objective + crossover through device function pointers)",
@@ -88,7 +88,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "-lms", "25"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except Exception:

@@ -293,11 +293,13 @@ static int launch_fast_inst(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 
 // Tile batch and occupancy target per shape, from the B200 sweeps in
 // profiles/r1_sweeps.md: packed bits run best with 16 parent loads in flight per
-// lane at 2 blocks/SM, f32 rows (more ALU work per byte) with 8 at 3 blocks/SM.
+// lane at 2 blocks/SM (the group width hardly matters: 8 lanes x 8 tiles 71.9 us,
+// 4 lanes x 2 blocks x 4 tiles 73.1 us, 8 lanes x 4 tiles 82 us per OneMax generation),
+// f32 rows (more ALU work per byte) with 8 at 3 blocks/SM.
 template <int ENC, int LOGG, int NB>
 struct TiledShape {
     static constexpr int G = 1 << LOGG;
-    static constexpr int TB = ENC == ENC_BITS ? (NB <= 2 ? (G < 4 ? G : 4) : 2) : (NB >= 2 ? 2 : (G < 4 ? G : 4));
+    static constexpr int TB = ENC == ENC_BITS ? (NB == 1 ? (G < 8 ? G : 8) : (NB == 2 ? (G < 4 ? G : 4) : 2)) : (NB >= 2 ? 2 : (G < 4 ? G : 4));
     static constexpr int MINB = ENC == ENC_BITS ? 2 : 3;
 };
 
@@ -368,18 +370,15 @@ static int launch_staged(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 #undef ST
 }
 
-// Shapes with a compile-time tiling.  f32 rows keep the oracle's canonical group
-// (G = min(32, pow2ceil(blocks)) lanes, NB = blocks per lane up to 4).  Packed bits
-// have an order-free integer score, so they use half as many lanes with two blocks
-// each (fewer shuffles and reductions per child).  Anything larger takes the
-// generic kernel.
+// Shapes with a compile-time tiling: G = min(32, pow2ceil(blocks)) lanes per child (the
+// oracle's canonical group for f32 scores), NB = blocks per lane up to 4.  Anything
+// larger takes the generic kernel.
 template <int ENC, int OBJ>
 static int launch_tiled(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
     const uint32_t nblk = p->stride >> 2;
     if (c->force_generic) return 1;
     uint32_t G = p->group;
-    if (ENC == ENC_BITS && nblk >= 2 && nblk <= 32) G = p->group / 2;  // pow2ceil(nblk) / 2 lanes, two blocks each
     const uint32_t NBr = (nblk + G - 1) / G;
 #define TL(L, N) return launch_tiled_inst<ENC, OBJ, L, N>(c, p, a)
     if (NBr == 1) {
