@@ -126,11 +126,6 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def make_solver(pg, w, seed, tsp=None):
-    g = pg.PGA(seed=seed)
-    return g
-
-
 def configure(pg, g, w):
     if w.get("builtin"):
         g.set_builtin_objective(getattr(pg, "OBJ_" + w["builtin"]))
