@@ -42,6 +42,33 @@ def test_select_top_matches_oracle(pga, oracle, n, k, kind):
         assert np.array_equal(got, want), (kind, worst)
 
 
+def test_select_top_large_population_uses_the_multi_launch_path(pga, oracle):
+    # 2^22 scores do not fit the cooperative single-launch select: the 5-launch path ranks them
+    n = 1 << 22
+    rng = np.random.default_rng(5)
+    s = rng.integers(300, 700, size=n).astype(np.float32)
+    g = pga(1)
+    p = g.create_population(n, 8)
+    g.set_objective_function("sum_obj")
+    p.set_scores(s)
+    for worst in (False, True):
+        assert np.array_equal(g.select_top(p, 41943, worst=worst), oracle.select_top(s, 41943, worst=worst))
+
+
+@pytest.mark.parametrize("n,k", [(1000, 10), (70000, 700), (1 << 20, 10485)])
+def test_select_top_multi_launch_path_small_sizes(pga, oracle, monkeypatch, n, k):
+    monkeypatch.setenv("PGA_NO_COOP", "1")
+    rng = np.random.default_rng(n)
+    s = rng.integers(0, 50, size=n).astype(np.float32)
+    s[rng.integers(0, n, size=n // 9)] = np.nan
+    g = pga(1)
+    p = g.create_population(n, 8)
+    g.set_objective_function("sum_obj")
+    p.set_scores(s)
+    for worst in (False, True):
+        assert np.array_equal(g.select_top(p, k, worst=worst), oracle.select_top(s, k, worst=worst))
+
+
 def make_islands(pga, oracle, seed, count, size, length, *, bits, topology, delay):
     g = pga(seed)
     o = oracle.Oracle(seed, threads=8)

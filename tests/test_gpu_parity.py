@@ -152,6 +152,24 @@ def test_tsp_demo(pga, oracle, tsp_matrix):
     o.close()
 
 
+def test_tsp_hooks_lockstep_at_scale(pga, oracle, tsp_matrix):
+    # config 4 (test3 hooks) at 2^17 individuals: one lock-step generation from a GPU state
+    n = 1 << 17
+    g, o, gp, op = setup_pair(pga, oracle, 21, n, 100, obj="tsp_obj", xover="tsp_crossover")
+    g.tsp_load(tsp_matrix)
+    o.tsp_load(tsp_matrix)
+    g.run(3)
+    op.set_genes(gp.genes())
+    op.set_epoch(gp.epoch)
+    gp.capture_selection(True)
+    g.run(1)
+    o.run(1)
+    assert np.array_equal(gp.selection(), op.selection())
+    assert same_bits(gp.genes(), op.genes())
+    assert same_bits(gp.scores(), op.scores())
+    o.close()
+
+
 # ---- config 2: OneMax on packed bits -----------------------------------------------
 
 @pytest.mark.parametrize("size,bits,gens", [(1 << 14, 1024, 100), (1000, 1000, 10), (77, 33, 6), (50, 4, 4), (300, 5000, 4)])
