@@ -48,6 +48,13 @@ KERNELS = {
 }
 
 
+FABRIC_NOTE = {
+    "onemax": "bound by SM<->L2 sector throughput, not HBM: 516 B per child cross L2 (4 score-gather sectors + 2 parents + child) "
+              "= 539 MB per launch at ~7.8 TB/s (ncu, profiles/r1_sweeps.md); that caps frac near 0.59",
+    "rastrigin": "HBM-bound: 3 population passes of DRAM traffic (2 gathered parents + 1 child) = 3.19 GB per launch at 93 % of the measured peak",
+}
+
+
 def genome_bytes(w):
     return w["length"] // 8 if w["bits"] else w["length"] * 4
 
@@ -359,7 +366,8 @@ def main():
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(args.workload), "kernel": KERNELS[args.workload],
                      "algorithmic_bytes_per_launch": 2 * w["size"] * gb, "avg_launch_ms": kernel_ms / n_launch,
-                     "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0},
+                     "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
+                     "note": FABRIC_NOTE.get(args.workload)},
     }
     if rank == 0 and not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline(w)                  # all host cores (OpenMP over individuals)
