@@ -166,8 +166,9 @@ __device__ __forceinline__ void fence_async_smem()
 }
 
 // ---- built-in objectives --------------------------------------------------
-// Operation order is part of the specification (oracle/pga_oracle.c,
-// opga_builtin_objective_f32): explicit _rn intrinsics keep nvcc from contracting.
+// Operation order is part of the specification ("canonical reduction
+// shape"): explicit _rn intrinsics keep nvcc from contracting, so float scores are
+// reproducible bit for bit on any conforming implementation.
 enum : int { OBJ_HOOK = 0, OBJ_SUM = 1, OBJ_RASTRIGIN = 2, OBJ_SPHERE = 3, OBJ_ONEMAX = 4 };
 
 __device__ __forceinline__ float cos2pi(float x)

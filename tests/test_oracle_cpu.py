@@ -197,3 +197,21 @@ def test_migration_count_matches_oracle(oracle):
     import libpga_b200 as pg
     for size, pct in ((1 << 22, 1.0), (1000, 2.5), (100, 0.0), (100, -1.0), (100, 150.0), (7, 33.3)):
         assert pg.migration_count(size, pct) == oracle.lib().opga_migration_count(size, pct)
+
+
+def test_missing_extension_fails_loudly(monkeypatch):
+    # no CPU fallback: without the built library the product refuses to load
+    from libpga_b200 import _lib
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "SO_PATH", os.path.join(ROOT, "libpga_b200", "does_not_exist.so"))
+    with pytest.raises(RuntimeError, match="not built"):
+        _lib.load()
+
+
+def test_product_never_touches_the_oracle():
+    # the oracle is test infrastructure: nothing under libpga_b200/ may import, load or name it
+    import glob
+    for path in glob.glob(os.path.join(ROOT, "libpga_b200", "**", "*"), recursive=True):
+        if os.path.isfile(path) and path.endswith((".py", ".c", ".cu", ".cuh", ".h")):
+            text = open(path).read()
+            assert "pyoracle" not in text and "pga_oracle" not in text and "opga_" not in text, path
