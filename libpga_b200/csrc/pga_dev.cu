@@ -86,6 +86,13 @@ struct pgadev_pop {
         (ctx)->launches += 1;          \
     } while (0)
 
+// every call works on the solver's own device, whatever the caller made current since pga_init
+static inline void use_device(pgadev_ctx* c)
+{
+    int d = -1;
+    if (cudaGetDevice(&d) == cudaSuccess && d != c->device) CCE(cudaSetDevice(c->device));
+}
+
 static uint32_t grid_for(uint64_t work_items, uint32_t per_block, uint32_t cap)
 {
     uint64_t g = (work_items + per_block - 1) / per_block;
@@ -149,13 +156,14 @@ extern "C" void pgadev_ctx_set_stream(pgadev_ctx* c, void* s) { c->stream = s ? 
 
 extern "C" void pgadev_ctx_sync(pgadev_ctx* c)
 {
+    use_device(c);
     CCE(cudaStreamSynchronize(c->stream));
     CCE(cudaStreamSynchronize(c->side));
 }
 
 extern "C" unsigned long long pgadev_ctx_launches(pgadev_ctx* c) { return c->launches; }
-extern "C" void pgadev_timer_start(pgadev_ctx* c) { CCE(cudaEventRecord(c->t0, c->stream)); }
-extern "C" void pgadev_timer_stop(pgadev_ctx* c) { CCE(cudaEventRecord(c->t1, c->stream)); }
+extern "C" void pgadev_timer_start(pgadev_ctx* c) { use_device(c); CCE(cudaEventRecord(c->t0, c->stream)); }
+extern "C" void pgadev_timer_stop(pgadev_ctx* c) { use_device(c); CCE(cudaEventRecord(c->t1, c->stream)); }
 extern "C" float pgadev_timer_ms(pgadev_ctx* c)
 {
     float ms = 0.f;
@@ -168,6 +176,7 @@ extern "C" float pgadev_timer_ms(pgadev_ctx* c)
 
 extern "C" pgadev_pop* pgadev_pop_create(pgadev_ctx* c, uint64_t size, uint32_t genome_len, int encoding)
 {
+    use_device(c);
     pgadev_pop* p = (pgadev_pop*)calloc(1, sizeof(*p));
     if (!p) return NULL;
     p->n = size;
@@ -197,7 +206,7 @@ extern "C" pgadev_pop* pgadev_pop_create(pgadev_ctx* c, uint64_t size, uint32_t 
 
 extern "C" void pgadev_pop_destroy(pgadev_ctx* c, pgadev_pop* p)
 {
-    (void)c;
+    use_device(c);
     if (!p) return;
     for (int i = 0; i < 2; ++i) {
         if (p->genes[i]) CCE(cudaFree(p->genes[i]));
@@ -231,6 +240,7 @@ static DrawCtx make_draw(uint64_t seed, uint32_t island, uint32_t epoch)
 
 extern "C" void pgadev_pop_init_random(pgadev_ctx* c, pgadev_pop* p, uint64_t seed, uint32_t island)
 {
+    use_device(c);
     if (p->n == 0) return;
     const uint64_t blocks16 = p->n * (p->stride >> 2);
     const uint32_t grid = grid_for(blocks16, 256, (uint32_t)c->sm_count * 16u);
@@ -244,7 +254,7 @@ extern "C" void pgadev_pop_init_random(pgadev_ctx* c, pgadev_pop* p, uint64_t se
 
 extern "C" void pgadev_pop_capture_selection(pgadev_ctx* c, pgadev_pop* p, int enable)
 {
-    (void)c;
+    use_device(c);
     if (enable && !p->sel) CCE(cudaMalloc((void**)&p->sel, (size_t)(p->n ? p->n : 1) * 2 * sizeof(int32_t)));
     p->capture = enable;
 }
@@ -427,6 +437,7 @@ static int launch_fast_ph(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a, uint32
 
 extern "C" int pgadev_launch(pgadev_ctx* c, pgadev_pop* p, const pgadev_step* st)
 {
+    use_device(c);
     if (p->n == 0) return 0;
     const uint32_t ph = st->phases;
     if (ph != PH_FUSED && ph != PH_EVALUATE && ph != PH_CROSSOVER && ph != PH_MUTATE) return PGAX_EINVAL;
@@ -489,6 +500,7 @@ extern "C" int pgadev_launch(pgadev_ctx* c, pgadev_pop* p, const pgadev_step* st
 
 extern "C" void pgadev_best(pgadev_ctx* c, pgadev_pop* p, int reduced_in_kernel, uint64_t* index, float* score)
 {
+    use_device(c);
     if (!reduced_in_kernel) {
         const uint32_t grid = grid_for(p->n, 256 * 8, (uint32_t)c->sm_count * 8u);
         reduce_best<<<grid, 256, 0, c->stream>>>(p->score[p->sidx], (uint32_t)p->n, p->best, p->best_seq & 3u);
@@ -541,16 +553,19 @@ static void copy_rows(pgadev_ctx* c, pgadev_pop* p, uint32_t* dev_rows, void* ho
 
 extern "C" void pgadev_upload_rows(pgadev_ctx* c, pgadev_pop* p, const void* host, int next_gen)
 {
+    use_device(c);
     copy_rows(c, p, p->genes[p->gidx ^ (next_gen ? 1 : 0)], (void*)host, true);
 }
 
 extern "C" void pgadev_download_rows(pgadev_ctx* c, pgadev_pop* p, void* host, int next_gen)
 {
+    use_device(c);
     copy_rows(c, p, p->genes[p->gidx ^ (next_gen ? 1 : 0)], host, false);
 }
 
 extern "C" void pgadev_download_row(pgadev_ctx* c, pgadev_pop* p, uint64_t index, void* host_words)
 {
+    use_device(c);
     CCE(cudaMemcpyAsync(host_words, p->genes[p->gidx] + index * p->stride, (size_t)p->row_words * 4u, cudaMemcpyDeviceToHost,
                         c->stream));
     CCE(cudaStreamSynchronize(c->stream));
@@ -558,18 +573,21 @@ extern "C" void pgadev_download_row(pgadev_ctx* c, pgadev_pop* p, uint64_t index
 
 extern "C" void pgadev_upload_scores(pgadev_ctx* c, pgadev_pop* p, const float* host)
 {
+    use_device(c);
     CCE(cudaMemcpyAsync(p->score[p->sidx], host, p->n * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     CCE(cudaStreamSynchronize(c->stream));
 }
 
 extern "C" void pgadev_download_scores(pgadev_ctx* c, pgadev_pop* p, float* host)
 {
+    use_device(c);
     CCE(cudaMemcpyAsync(host, p->score[p->sidx], p->n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
     CCE(cudaStreamSynchronize(c->stream));
 }
 
 extern "C" int pgadev_download_selection(pgadev_ctx* c, pgadev_pop* p, int32_t* host_pairs)
 {
+    use_device(c);
     if (!p->sel) return PGAX_EINVAL;
     CCE(cudaMemcpyAsync(host_pairs, p->sel, p->n * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
     CCE(cudaStreamSynchronize(c->stream));
@@ -632,6 +650,7 @@ extern "C" void pgadev_route_to_side(pgadev_ctx* c, int on) { c->route_side = on
 
 extern "C" void pgadev_select_top(pgadev_ctx* c, pgadev_pop* p, uint64_t k, int worst, int slot)
 {
+    use_device(c);
     if (k == 0 || p->n == 0) return;
     if (k > p->n) k = p->n;
     if (!p->topk[slot]) {
@@ -665,6 +684,7 @@ extern "C" void pgadev_select_top(pgadev_ctx* c, pgadev_pop* p, uint64_t k, int 
 
 extern "C" void pgadev_download_top(pgadev_ctx* c, pgadev_pop* p, int slot, uint64_t k, uint32_t* host_idx)
 {
+    use_device(c);
     CCE(cudaMemcpyAsync(host_idx, p->idx[slot], k * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
     CCE(cudaStreamSynchronize(c->stream));
 }
@@ -685,10 +705,11 @@ static void ensure_boxes(pgadev_ctx* c, pgadev_pop* p, uint64_t k)
 
 static size_t box_words(const pgadev_pop* p, uint64_t k) { return (size_t)k * (p->stride + 1u); }
 
-extern "C" void pgadev_reserve_boxes(pgadev_ctx* c, pgadev_pop* p, uint64_t k) { ensure_boxes(c, p, k); }
+extern "C" void pgadev_reserve_boxes(pgadev_ctx* c, pgadev_pop* p, uint64_t k) { use_device(c); ensure_boxes(c, p, k); }
 
 extern "C" void pgadev_pack_emigrants(pgadev_ctx* c, pgadev_pop* p, uint64_t k)
 {
+    use_device(c);
     ensure_boxes(c, p, k);
     const uint32_t grid = grid_for(k * (p->stride >> 2), 256, (uint32_t)c->sm_count * 8u);
     pack_rows<<<grid, 256, 0, work_stream(c)>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[0], (uint32_t)k, p->stride, p->outbox);
@@ -697,11 +718,13 @@ extern "C" void pgadev_pack_emigrants(pgadev_ctx* c, pgadev_pop* p, uint64_t k)
 
 extern "C" void pgadev_transfer_local(pgadev_ctx* c, pgadev_pop* src, pgadev_pop* dst, uint64_t k)
 {
+    use_device(c);
     CCE(cudaMemcpyAsync(dst->inbox, src->outbox, box_words(src, k) * 4u, cudaMemcpyDeviceToDevice, c->side));
 }
 
 extern "C" void pgadev_unpack_immigrants(pgadev_ctx* c, pgadev_pop* p, uint64_t k)
 {
+    use_device(c);
     const uint32_t grid = grid_for(k * (p->stride >> 2), 256, (uint32_t)c->sm_count * 8u);
     unpack_rows<<<grid, 256, 0, c->stream>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[1], (uint32_t)k, p->stride, p->inbox);
     LAUNCH_CHECK(c);
@@ -709,6 +732,7 @@ extern "C" void pgadev_unpack_immigrants(pgadev_ctx* c, pgadev_pop* p, uint64_t 
 
 extern "C" void pgadev_side_after_main(pgadev_ctx* c)
 {
+    use_device(c);
     CCE(cudaEventRecord(c->ev_main, c->stream));
     CCE(cudaStreamWaitEvent(c->side, c->ev_main, 0));
 }
@@ -720,6 +744,7 @@ extern "C" void pgadev_main_wait_packed(pgadev_ctx* c) { CCE(cudaStreamWaitEvent
 
 extern "C" void pgadev_main_after_side(pgadev_ctx* c)
 {
+    use_device(c);
     CCE(cudaEventRecord(c->ev_side, c->side));
     CCE(cudaStreamWaitEvent(c->stream, c->ev_side, 0));
 }
