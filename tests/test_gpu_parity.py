@@ -347,3 +347,43 @@ def test_seed_changes_everything_and_same_seed_repeats(pga):
         res.append(p.genes())
     assert same_bits(res[0], res[1])
     assert not same_bits(res[0], res[2])
+
+
+def test_null_hook_restores_default_operator(pga, tsp_matrix):
+    # include/pga.h:76,83: "if NULL, default random is used"
+    a = pga(8); b = pga(8)
+    pa = a.create_population(700, 100); pb = b.create_population(700, 100)
+    a.tsp_load(tsp_matrix)
+    for g in (a, b):
+        g.set_objective_function("sum_obj")
+    a.set_crossover_function("tsp_crossover")
+    a.set_crossover_function(None)
+    a.run(4); b.run(4)
+    assert same_bits(pa.genes(), pb.genes())
+
+
+def test_run_zero_generations_only_scores(pga, oracle):
+    g, o, gp, op = setup_pair(pga, oracle, 2, 500, 12, obj="sum_obj")
+    before = gp.genes()
+    g.run(0); o.run(0)                        # src/pga.cu:390: the trailing evaluate still happens
+    assert same_bits(gp.genes(), before)
+    assert same_bits(gp.scores(), op.scores())
+    o.close()
+
+
+def test_empty_population_is_harmless(pga):
+    g = pga(1)
+    p = g.create_population(0, 8)
+    assert p is not None and p.size == 0
+    g.set_objective_function("sum_obj")
+    g.run(3)
+    assert g.get_best(p) is None
+
+
+def test_get_best_top_longer_than_population(pga, oracle):
+    g, o, gp, op = setup_pair(pga, oracle, 2, 5, 8, obj="sum_obj")
+    g.run(1); o.run(1)
+    rows = g.get_best_top(gp, 9)
+    want = o.get_best_top(op, 9)
+    assert len(rows) == 5 and all(same_bits(x, y) for x, y in zip(rows, want))
+    o.close()
