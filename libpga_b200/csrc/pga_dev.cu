@@ -49,6 +49,7 @@ struct pgadev_ctx {
     int fast_blocks_per_sm_set;
     int force_generic;            // $PGA_FORCE_GENERIC=1: skip the compile-time tiled kernels
     int staged;                   // $PGA_STAGED=1: small rows take the cp.async-staged kernel instead
+    int no_hook_split;            // $PGA_NO_HOOK_SPLIT=1: generations with hooks are always one launch
     int no_coop;                  // $PGA_NO_COOP=1: rank with the 5-launch select instead of the cooperative kernel
     uint32_t reserve_now;         // SMs' worth of blocks the current launch leaves free (pgadev_step.reserve_sms)
 };
@@ -75,6 +76,9 @@ struct pgadev_pop {
     uint32_t nb;
     uint32_t* idx[2];
     uint64_t idx_cap[2];
+    // hook path: fused launch or crossover+mutate then evaluate (see launch_hooks_fused)
+    int hook_mode, hook_trials;
+    float hook_ms[2];
     // migration boxes
     uint32_t *outbox, *inbox;
     uint64_t box_cap;
@@ -130,6 +134,7 @@ extern "C" pgadev_ctx* pgadev_ctx_create(void)
     c->fast_blocks_per_sm_set = e && atoi(e) > 0;
     c->force_generic = (e = getenv("PGA_FORCE_GENERIC")) ? atoi(e) : 0;
     c->staged = (e = getenv("PGA_STAGED")) ? atoi(e) : 0;
+    c->no_hook_split = (e = getenv("PGA_NO_HOOK_SPLIT")) ? atoi(e) : 0;
     c->no_coop = (e = getenv("PGA_NO_COOP")) ? atoi(e) : 0;
     const char* stack = getenv("PGA_STACK_BYTES");  // device stack for deep user hooks
     if (stack && atoi(stack) > 0) CCE(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(stack)));
@@ -290,6 +295,45 @@ static int launch_hooks(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
     generation_hooks<PH><<<grid, T, smem_final, c->stream>>>(a);
     LAUNCH_CHECK(c);
     return 0;
+}
+
+// A generation with a crossover hook stages four rows per thread in shared memory (child,
+// both parents, the rand row), which leaves 4 warps per SM.  When the objective hook is the
+// expensive part (test3: 10^4 compare iterations per evaluation) it pays to score the
+// children in a second launch that holds one row per thread and so runs 4x the threads:
+// at 2^20 x 100 the fused launch takes 20.2 ms, crossover+mutate then evaluate 16.5 ms.
+// Which is faster depends on the user's hooks, so the first two generations are timed
+// (one each way) and the population keeps the winner.  Results are identical either way.
+static int launch_hooks_split(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+{
+    int rc = launch_hooks<PH_CROSSOVER | PH_MUTATE>(c, p, a);
+    if (rc != 0) return rc;
+    GenArgs e = a;
+    e.cur = a.nxt;  // the evaluate phase scores "current_gen": point it at the children
+    return launch_hooks<PH_EVALUATE>(c, p, e);
+}
+
+static int launch_hooks_fused(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+{
+    const bool candidate = a.xov != nullptr && a.objective == OBJ_HOOK && !c->no_hook_split && p->n >= 4096;
+    if (!candidate) return launch_hooks<PH_FUSED>(c, p, a);
+    if (p->hook_mode == 1) return launch_hooks<PH_FUSED>(c, p, a);
+    if (p->hook_mode == 2) return launch_hooks_split(c, p, a);
+    // undecided: time this generation one way
+    const int trial = p->hook_trials;  // 0 = fused, 1 = split
+    cudaEvent_t e0, e1;
+    CCE(cudaEventCreate(&e0));
+    CCE(cudaEventCreate(&e1));
+    CCE(cudaEventRecord(e0, c->stream));
+    const int rc = trial == 0 ? launch_hooks<PH_FUSED>(c, p, a) : launch_hooks_split(c, p, a);
+    CCE(cudaEventRecord(e1, c->stream));
+    CCE(cudaEventSynchronize(e1));
+    CCE(cudaEventElapsedTime(&p->hook_ms[trial], e0, e1));
+    CCE(cudaEventDestroy(e0));
+    CCE(cudaEventDestroy(e1));
+    p->hook_trials += 1;
+    if (p->hook_trials == 2) p->hook_mode = p->hook_ms[1] < p->hook_ms[0] ? 2 : 1;
+    return rc;
 }
 
 template <int ENC, uint32_t PH, int OBJ>
@@ -478,7 +522,7 @@ extern "C" int pgadev_launch(pgadev_ctx* c, pgadev_pop* p, const pgadev_step* st
         if (uses_xov || uses_mut || hook_obj) {
             if (hook_obj && !a.obj) return PGAX_EINVAL;
             switch (ph) {
-                case PH_FUSED: rc = launch_hooks<PH_FUSED>(c, p, a); break;
+                case PH_FUSED: rc = launch_hooks_fused(c, p, a); break;
                 case PH_EVALUATE: rc = launch_hooks<PH_EVALUATE>(c, p, a); break;
                 case PH_CROSSOVER: rc = launch_hooks<PH_CROSSOVER>(c, p, a); break;
                 default: rc = launch_hooks<PH_MUTATE>(c, p, a); break;
