@@ -44,7 +44,7 @@ KERNELS = {
     "onemax": "generation_fused_tiled<ENC_BITS, OBJ_ONEMAX, LOGG=3, NB=1, TB=8>",
     "rastrigin": "generation_fused_tiled<ENC_F32, OBJ_RASTRIGIN, LOGG=5, NB=2, TB=2>",
     "test1": "generation_hooks<PH_FUSED> (user objective through a device function pointer)",
-    "tsp": "generation_hooks<PH_FUSED> (user objective + crossover through device function pointers)",
+    "tsp": "generation_hooks<CROSSOVER+MUTATE> then generation_hooks<EVALUATE> (user hooks through device function pointers; split chosen by timing)",
 }
 
 
