@@ -158,3 +158,25 @@ def test_evaluate_all_and_friends(pga, oracle):
         g.swap_generations(gp); o.swap_generations(op)
     g.evaluate_all(); o.evaluate_all()
     assert_islands_equal(gps, ops)
+
+
+def test_c5_island_size_full_trajectory(pga, oracle):
+    # BASELINE config 5 at its real island size: 2 islands x 2^22 x 1024 bits, ring, top 1 %
+    # (41 943 rows) chosen at generation 10 and landing at generation 11; the whole
+    # trajectory is replayed on the oracle
+    import os
+    n = 1 << 22
+    g = pga(42)
+    o = oracle.Oracle(42, threads=os.cpu_count() or 1)
+    gps = [g.create_population(n, 1024, encoding=pg.GENES_BITS) for _ in range(2)]
+    ops = [o.create_population(n, 1024, oracle.GENES_BITS) for _ in range(2)]
+    g.set_builtin_objective(pg.OBJ_ONEMAX); o.set_builtin_objective(oracle.OBJ_ONEMAX)
+    g.set_topology(pg.TOPO_RING); o.set_topology(oracle.TOPO_RING)
+    g.run_islands(12, 10, 1.0)
+    o.run_islands(12, 10, 1.0)
+    assert pg.migration_count(n, 1.0) == 41943
+    for gp, op in zip(gps, ops):
+        assert np.array_equal(gp.scores(), op.scores())
+        assert oracle.digest(gp.genes()) == oracle.digest(op.genes())
+        assert g.best(gp) == o.best_index(op)
+    o.close()
