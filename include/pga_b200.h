@@ -180,6 +180,10 @@ int pgax_plan_exchange(uint64_t seed, uint32_t round, enum pgax_topology topolog
 float pgax_last_run_ms(pga_t *);
 /* Kernels launched by this solver so far. */
 unsigned long long pgax_kernel_launches(pga_t *);
+/* Bytes this solver has copied from the device to the host so far (results, scores,
+ * rows, index lists).  pga_get_best copies all N scores in the reference
+ * (src/pga.cu:219-220); here it is a 16-byte key and one row. */
+unsigned long long pgax_bytes_to_host(pga_t *);
 
 /* ---- the reference's demo hooks, compiled into the shared library --------- */
 

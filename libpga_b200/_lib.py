@@ -73,6 +73,7 @@ SIGNATURES = {
     "pgax_plan_exchange": (_i32, [_u64, _u32, _i32, _i32, _ui, _vp, _ui]),
     "pgax_last_run_ms": (_f32, [_vp]),
     "pgax_kernel_launches": (C.c_ulonglong, [_vp]),
+    "pgax_bytes_to_host": (C.c_ulonglong, [_vp]),
     "pgax_demo_hook": (_vp, [C.c_char_p]),
     "pgax_demo_tsp_load": (_i32, [_vp, _i32]),
     "pgax_version": (C.c_char_p, []),

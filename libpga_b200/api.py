@@ -244,6 +244,10 @@ class PGA:
     def kernel_launches(self):
         return int(self.L.pgax_kernel_launches(self.h))
 
+    @property
+    def bytes_to_host(self):
+        return int(self.L.pgax_bytes_to_host(self.h))
+
 
 def dist_unique_id():
     buf = (C.c_ubyte * 128)()

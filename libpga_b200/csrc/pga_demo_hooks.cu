@@ -62,7 +62,25 @@ __device__ void demo_tsp_crossover(gene* p1, gene* p2, gene* child, float* rnd, 
     }
 }
 
+// Test hooks with no counterpart in the reference's demos.  A crossover that writes
+// only the even genes: the odd ones keep what the child row held before the call, which
+// the reference defines as the stale next_gen row (src/pga.cu:302).
+__device__ void demo_even_crossover(gene* p1, gene* p2, gene* child, float* rnd, unsigned len)
+{
+    for (unsigned k = 0; k < len; k += 2) child[k] = rnd[k] > 0.5f ? p1[k] : p2[k];
+}
+
+// A mutation hook that reads its whole rand row: every gene moves towards the draw with
+// probability 1/8.
+__device__ void demo_blend_mutate(gene* g, float* rnd, unsigned len)
+{
+    for (unsigned k = 0; k < len; ++k)
+        if (rnd[k] < 0.125f) g[k] = 0.5f * (g[k] + rnd[(k + 1) % len]);
+}
+
 __device__ obj_f demo_sum_obj_ptr = demo_sum_obj;
+__device__ crossover_f demo_even_crossover_ptr = demo_even_crossover;
+__device__ mutate_f demo_blend_mutate_ptr = demo_blend_mutate;
 __device__ obj_f demo_knapsack_obj_ptr = demo_knapsack_obj;
 __device__ obj_f demo_tsp_obj_ptr = demo_tsp_obj;
 __device__ crossover_f demo_tsp_crossover_ptr = demo_tsp_crossover;
@@ -83,6 +101,8 @@ extern "C" void* pgax_demo_hook(const char* name)
     else if (!strcmp(name, "knapsack_obj")) check(cudaMemcpyFromSymbol(&fn, demo_knapsack_obj_ptr, sizeof(fn)), __LINE__);
     else if (!strcmp(name, "tsp_obj")) check(cudaMemcpyFromSymbol(&fn, demo_tsp_obj_ptr, sizeof(fn)), __LINE__);
     else if (!strcmp(name, "tsp_crossover")) check(cudaMemcpyFromSymbol(&fn, demo_tsp_crossover_ptr, sizeof(fn)), __LINE__);
+    else if (!strcmp(name, "even_crossover")) check(cudaMemcpyFromSymbol(&fn, demo_even_crossover_ptr, sizeof(fn)), __LINE__);
+    else if (!strcmp(name, "blend_mutate")) check(cudaMemcpyFromSymbol(&fn, demo_blend_mutate_ptr, sizeof(fn)), __LINE__);
     return fn;
 }
 

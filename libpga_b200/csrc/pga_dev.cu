@@ -42,6 +42,7 @@ struct pgadev_ctx {
     int route_side;  // ranking and packing go to the side stream (emigrant selection overlaps the next generation)
     cudaEvent_t ev_main, ev_side, ev_packed, t0, t1;
     unsigned long long launches;
+    unsigned long long d2h_bytes;  // bytes copied device -> host by this solver
     ncclComm_t comm;
     int hook_threads;  // $PGA_HOOK_THREADS override, 0 = automatic
     // tuning knobs, settable from the environment for on-device experiments
@@ -52,6 +53,8 @@ struct pgadev_ctx {
     int no_hook_split;            // $PGA_NO_HOOK_SPLIT=1: generations with hooks are always one launch
     int no_coop;                  // $PGA_NO_COOP=1: rank with the 5-launch select instead of the cooperative kernel
     uint32_t reserve_now;         // SMs' worth of blocks the current launch leaves free (pgadev_step.reserve_sms)
+    int l2_persist;               // $PGA_L2_PERSIST: 1 = children being written persist in L2, 2 = the parents' buffer does (experiment)
+    size_t l2_window_max;
 };
 
 struct pgadev_pop {
@@ -75,6 +78,7 @@ struct pgadev_pop {
     uint32_t *blk_gt[2], *blk_eq[2];
     uint32_t nb;
     uint32_t* idx[2];
+    float* idx_score[2];  // scores of the listed individuals (pgadev_download_top_scores)
     uint64_t idx_cap[2];
     // hook path: fused launch or crossover+mutate then evaluate (see launch_hooks_fused)
     int hook_mode, hook_trials;
@@ -82,6 +86,9 @@ struct pgadev_pop {
     // migration boxes
     uint32_t *outbox, *inbox;
     uint64_t box_cap;
+    // host <-> device staging for padded rows
+    uint32_t* stage;
+    size_t stage_bytes;
 };
 
 #define LAUNCH_CHECK(ctx)              \
@@ -136,6 +143,11 @@ extern "C" pgadev_ctx* pgadev_ctx_create(void)
     c->staged = (e = getenv("PGA_STAGED")) ? atoi(e) : 0;
     c->no_hook_split = (e = getenv("PGA_NO_HOOK_SPLIT")) ? atoi(e) : 0;
     c->no_coop = (e = getenv("PGA_NO_COOP")) ? atoi(e) : 0;
+    c->l2_persist = (e = getenv("PGA_L2_PERSIST")) ? atoi(e) : 0;
+    if (c->l2_persist) {
+        CCE(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize));
+        c->l2_window_max = (size_t)prop.accessPolicyMaxWindowSize;
+    }
     const char* stack = getenv("PGA_STACK_BYTES");  // device stack for deep user hooks
     if (stack && atoi(stack) > 0) CCE(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(stack)));
     return c;
@@ -167,6 +179,7 @@ extern "C" void pgadev_ctx_sync(pgadev_ctx* c)
 }
 
 extern "C" unsigned long long pgadev_ctx_launches(pgadev_ctx* c) { return c->launches; }
+extern "C" unsigned long long pgadev_ctx_d2h_bytes(pgadev_ctx* c) { return c->d2h_bytes; }
 extern "C" void pgadev_timer_start(pgadev_ctx* c) { use_device(c); CCE(cudaEventRecord(c->t0, c->stream)); }
 extern "C" void pgadev_timer_stop(pgadev_ctx* c) { use_device(c); CCE(cudaEventRecord(c->t1, c->stream)); }
 extern "C" float pgadev_timer_ms(pgadev_ctx* c)
@@ -203,6 +216,9 @@ extern "C" pgadev_pop* pgadev_pop_create(pgadev_ctx* c, uint64_t size, uint32_t 
             return NULL;
         }
         CCE(cudaMemsetAsync(p->score[i], 0, score_bytes, c->stream));
+        // next_gen starts zeroed: a crossover hook that does not write every gene sees this
+        // row (the reference leaves it uninitialised, src/pga.cu:109, :302)
+        CCE(cudaMemsetAsync(p->genes[i], 0, gene_bytes, c->stream));
     }
     CCE(cudaMalloc((void**)&p->best, 4 * sizeof(unsigned long long)));
     CCE(cudaMemsetAsync(p->best, 0, 4 * sizeof(unsigned long long), c->stream));
@@ -217,6 +233,7 @@ extern "C" void pgadev_pop_destroy(pgadev_ctx* c, pgadev_pop* p)
         if (p->genes[i]) CCE(cudaFree(p->genes[i]));
         if (p->score[i]) CCE(cudaFree(p->score[i]));
         if (p->idx[i]) CCE(cudaFree(p->idx[i]));
+        if (p->idx_score[i]) CCE(cudaFree(p->idx_score[i]));
     }
     if (p->best) CCE(cudaFree(p->best));
     if (p->sel) CCE(cudaFree(p->sel));
@@ -228,6 +245,7 @@ extern "C" void pgadev_pop_destroy(pgadev_ctx* c, pgadev_pop* p)
     }
     if (p->outbox) CCE(cudaFree(p->outbox));
     if (p->inbox) CCE(cudaFree(p->inbox));
+    if (p->stage) CCE(cudaFree(p->stage));
     free(p);
 }
 
@@ -270,6 +288,7 @@ extern "C" void pgadev_swap_scores(pgadev_pop* p) { p->sidx ^= 1; }
 // ---- kernel dispatch ----------------------------------------------------------------
 
 #define SMEM_LIMIT (227u * 1024u)
+#define MAX_DEVICES 64
 
 template <uint32_t PH>
 static int launch_hooks(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
@@ -319,13 +338,23 @@ static int launch_hooks_fused(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
     if (!candidate) return launch_hooks<PH_FUSED>(c, p, a);
     if (p->hook_mode == 1) return launch_hooks<PH_FUSED>(c, p, a);
     if (p->hook_mode == 2) return launch_hooks_split(c, p, a);
-    // undecided: time this generation one way
+    // a stream that is being captured cannot be timed or waited on: keep the single launch
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(c->stream, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) {
+        cudaGetLastError();
+        return launch_hooks<PH_FUSED>(c, p, a);
+    }
+    // undecided: time this generation one way.  The launch is idempotent (it reads the
+    // current generation and writes the next), so it runs once untimed first: the timed
+    // run then pays no module-load or first-launch cost, whichever variant goes first.
     const int trial = p->hook_trials;  // 0 = fused, 1 = split
+    int rc = trial == 0 ? launch_hooks<PH_FUSED>(c, p, a) : launch_hooks_split(c, p, a);
+    if (rc != 0) return rc;
     cudaEvent_t e0, e1;
     CCE(cudaEventCreate(&e0));
     CCE(cudaEventCreate(&e1));
     CCE(cudaEventRecord(e0, c->stream));
-    const int rc = trial == 0 ? launch_hooks<PH_FUSED>(c, p, a) : launch_hooks_split(c, p, a);
+    rc = trial == 0 ? launch_hooks<PH_FUSED>(c, p, a) : launch_hooks_split(c, p, a);
     CCE(cudaEventRecord(e1, c->stream));
     CCE(cudaEventSynchronize(e1));
     CCE(cudaEventElapsedTime(&p->hook_ms[trial], e0, e1));
@@ -361,12 +390,14 @@ template <int ENC, int OBJ, int LOGG, int NB, bool EXACT>
 static int launch_tiled_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
     constexpr int TB = TiledShape<ENC, LOGG, NB>::TB, MINB = TiledShape<ENC, LOGG, NB>::MINB;
-    static int configured_for = -1;
-    static int blocks_per_sm = 2;
-    if (configured_for != c->device) {
+    // occupancy per device ordinal: a second thread or solver on another device reads its
+    // own entry (a racing first use writes the same value twice)
+    static int occupancy[MAX_DEVICES];
+    int blocks_per_sm = occupancy[c->device % MAX_DEVICES];
+    if (blocks_per_sm == 0) {
         CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, generation_fused_tiled<ENC, OBJ, LOGG, NB, TB, EXACT, MINB>, 256, 0));
         if (blocks_per_sm < 1) blocks_per_sm = 1;
-        configured_for = c->device;
+        occupancy[c->device % MAX_DEVICES] = blocks_per_sm;
     }
     // exactly one resident wave (a partial second wave costs a full kernel tail), minus
     // the blocks held back so that side-stream work can run beside this launch
@@ -393,15 +424,15 @@ static int launch_staged_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
     constexpr int WARPS = 4;
     constexpr size_t smem = (size_t)WARPS * 2u * 32u * (16u << LOGG);
-    static int configured_for = -1;
-    static int blocks_per_sm = 1;
-    if (configured_for != c->device) {
+    static int occupancy[MAX_DEVICES];
+    int blocks_per_sm = occupancy[c->device % MAX_DEVICES];
+    if (blocks_per_sm == 0) {
         CCE(cudaFuncSetAttribute(generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS, MINB>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS, MINB>,
                                                           WARPS * 32, smem));
         if (blocks_per_sm < 1) blocks_per_sm = 1;
-        configured_for = c->device;
+        occupancy[c->device % MAX_DEVICES] = blocks_per_sm;
     }
     const uint32_t grid = grid_for(p->n, WARPS * 32u, (uint32_t)(c->sm_count * blocks_per_sm));
     generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS, MINB><<<grid, WARPS * 32, smem, c->stream>>>(a);
@@ -508,6 +539,19 @@ extern "C" int pgadev_launch(pgadev_ctx* c, pgadev_pop* p, const pgadev_step* st
     a.mut = (mutate_fn)st->mutate_hook;
     a.xov = (crossover_fn)st->crossover_hook;
 
+    if (c->l2_persist && ph == PH_FUSED) {
+        // experiment: ask L2 to keep one generation buffer resident (access-policy window on the stream)
+        cudaStreamAttrValue v;
+        memset(&v, 0, sizeof(v));
+        size_t bytes = (size_t)p->n * p->stride * 4u;
+        if (bytes > c->l2_window_max) bytes = c->l2_window_max;
+        v.accessPolicyWindow.base_ptr = (void*)((c->l2_persist & 3) == 1 ? (const void*)a.nxt : (const void*)a.cur);
+        v.accessPolicyWindow.num_bytes = bytes;
+        v.accessPolicyWindow.hitRatio = (c->l2_persist & 4) ? 0.6f : 1.0f;
+        v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        CCE(cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &v));
+    }
     const bool uses_xov = (ph & PH_CROSSOVER) && a.xov, uses_mut = (ph & PH_MUTATE) && a.mut;
     const bool scores = (ph & PH_EVALUATE) != 0;
     int rc;
@@ -554,6 +598,7 @@ extern "C" void pgadev_best(pgadev_ctx* c, pgadev_pop* p, int reduced_in_kernel,
     unsigned long long key = 0;
     float first = 0.f;
     CCE(cudaMemcpyAsync(&key, p->best + ((p->best_seq - 1u) & 3u), sizeof(key), cudaMemcpyDeviceToHost, c->stream));
+    c->d2h_bytes += sizeof(key) + 2 * sizeof(float);
     CCE(cudaMemcpyAsync(&first, p->score[p->sidx], sizeof(float), cudaMemcpyDeviceToHost, c->stream));
     CCE(cudaStreamSynchronize(c->stream));
     // src/pga.cu:221-229 never displaces a NaN sitting at index 0
@@ -575,12 +620,17 @@ static void copy_rows(pgadev_ctx* c, pgadev_pop* p, uint32_t* dev_rows, void* ho
     const size_t host_bytes = (size_t)p->n * p->row_words * 4u;
     if (p->row_words == p->stride) {
         if (upload) CCE(cudaMemcpyAsync(dev_rows, host, host_bytes, cudaMemcpyHostToDevice, c->stream));
-        else CCE(cudaMemcpyAsync(host, dev_rows, host_bytes, cudaMemcpyDeviceToHost, c->stream));
+        else { CCE(cudaMemcpyAsync(host, dev_rows, host_bytes, cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += host_bytes; }
         CCE(cudaStreamSynchronize(c->stream));
         return;
     }
-    uint32_t* tmp;
-    CCE(cudaMalloc((void**)&tmp, host_bytes));
+    // unpadded staging copy of the rows, kept for the next transfer (freed with the population)
+    if (p->stage_bytes < host_bytes) {
+        if (p->stage) CCE(cudaFree(p->stage));
+        CCE(cudaMalloc((void**)&p->stage, host_bytes));
+        p->stage_bytes = host_bytes;
+    }
+    uint32_t* tmp = p->stage;
     const uint32_t grid = grid_for(p->n * p->stride, 256, (uint32_t)c->sm_count * 16u);
     if (upload) {
         CCE(cudaMemcpyAsync(tmp, host, host_bytes, cudaMemcpyHostToDevice, c->stream));
@@ -590,9 +640,9 @@ static void copy_rows(pgadev_ctx* c, pgadev_pop* p, uint32_t* dev_rows, void* ho
         repack_rows<<<grid, 256, 0, c->stream>>>(dev_rows, tmp, p->n, p->stride, p->row_words);
         LAUNCH_CHECK(c);
         CCE(cudaMemcpyAsync(host, tmp, host_bytes, cudaMemcpyDeviceToHost, c->stream));
+        c->d2h_bytes += host_bytes;
     }
     CCE(cudaStreamSynchronize(c->stream));
-    CCE(cudaFree(tmp));
 }
 
 extern "C" void pgadev_upload_rows(pgadev_ctx* c, pgadev_pop* p, const void* host, int next_gen)
@@ -612,6 +662,7 @@ extern "C" void pgadev_download_row(pgadev_ctx* c, pgadev_pop* p, uint64_t index
     use_device(c);
     CCE(cudaMemcpyAsync(host_words, p->genes[p->gidx] + index * p->stride, (size_t)p->row_words * 4u, cudaMemcpyDeviceToHost,
                         c->stream));
+    c->d2h_bytes += (size_t)p->row_words * 4u;
     CCE(cudaStreamSynchronize(c->stream));
 }
 
@@ -626,6 +677,7 @@ extern "C" void pgadev_download_scores(pgadev_ctx* c, pgadev_pop* p, float* host
 {
     use_device(c);
     CCE(cudaMemcpyAsync(host, p->score[p->sidx], p->n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    c->d2h_bytes += p->n * sizeof(float);
     CCE(cudaStreamSynchronize(c->stream));
 }
 
@@ -634,6 +686,7 @@ extern "C" int pgadev_download_selection(pgadev_ctx* c, pgadev_pop* p, int32_t* 
     use_device(c);
     if (!p->sel) return PGAX_EINVAL;
     CCE(cudaMemcpyAsync(host_pairs, p->sel, p->n * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    c->d2h_bytes += p->n * 2 * sizeof(int32_t);
     CCE(cudaStreamSynchronize(c->stream));
     return 0;
 }
@@ -645,7 +698,9 @@ static void ensure_index_list(pgadev_ctx* c, pgadev_pop* p, int slot, uint64_t k
     if (p->idx_cap[slot] >= k) return;
     pgadev_ctx_sync(c);
     if (p->idx[slot]) CCE(cudaFree(p->idx[slot]));
+    if (p->idx_score[slot]) CCE(cudaFree(p->idx_score[slot]));
     CCE(cudaMalloc((void**)&p->idx[slot], k * sizeof(uint32_t)));
+    CCE(cudaMalloc((void**)&p->idx_score[slot], k * sizeof(float)));
     p->idx_cap[slot] = k;
 }
 
@@ -656,12 +711,14 @@ static cudaStream_t work_stream(pgadev_ctx* c) { return c->route_side ? c->side 
 template <int E>
 static bool select_top_coop_e(pgadev_ctx* c, pgadev_pop* p, uint32_t k, int worst, int slot, cudaStream_t s)
 {
-    static int configured_for = -1;
-    static int blocks_per_sm = 0;
-    if (configured_for != c->device) {
+    static int occupancy[MAX_DEVICES];  // per device ordinal; -1 = the kernel does not fit
+    int blocks_per_sm = occupancy[c->device % MAX_DEVICES];
+    if (blocks_per_sm == 0) {
         CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, topk_select_coop<E>, 256, 0));
-        configured_for = c->device;
+        if (blocks_per_sm < 1) blocks_per_sm = -1;
+        occupancy[c->device % MAX_DEVICES] = blocks_per_sm;
     }
+    if (blocks_per_sm < 0) return false;
     const uint64_t per_block = 256ull * E;
     const uint64_t grid = (p->n + per_block - 1) / per_block;
     if (grid > (uint64_t)blocks_per_sm * (uint64_t)c->sm_count) return false;
@@ -730,6 +787,20 @@ extern "C" void pgadev_download_top(pgadev_ctx* c, pgadev_pop* p, int slot, uint
 {
     use_device(c);
     CCE(cudaMemcpyAsync(host_idx, p->idx[slot], k * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    c->d2h_bytes += k * sizeof(uint32_t);
+    CCE(cudaStreamSynchronize(c->stream));
+}
+
+// scores of the k listed individuals only: k floats cross PCIe, not the whole score array
+extern "C" void pgadev_download_top_scores(pgadev_ctx* c, pgadev_pop* p, int slot, uint64_t k, float* host_scores)
+{
+    use_device(c);
+    if (k == 0) return;
+    gather_scores<<<grid_for(k, 256, (uint32_t)c->sm_count * 8u), 256, 0, c->stream>>>(p->score[p->sidx], p->idx[slot], (uint32_t)k,
+                                                                                     p->idx_score[slot]);
+    LAUNCH_CHECK(c);
+    CCE(cudaMemcpyAsync(host_scores, p->idx_score[slot], k * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    c->d2h_bytes += k * sizeof(float);
     CCE(cudaStreamSynchronize(c->stream));
 }
 

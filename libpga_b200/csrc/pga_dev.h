@@ -45,6 +45,7 @@ void pgadev_ctx_destroy(pgadev_ctx *);
 void pgadev_ctx_set_stream(pgadev_ctx *, void *stream);
 void pgadev_ctx_sync(pgadev_ctx *);
 unsigned long long pgadev_ctx_launches(pgadev_ctx *);
+unsigned long long pgadev_ctx_d2h_bytes(pgadev_ctx *);
 /* event pair on the main stream around a region */
 void pgadev_timer_start(pgadev_ctx *);
 void pgadev_timer_stop(pgadev_ctx *);
@@ -81,6 +82,8 @@ int pgadev_download_selection(pgadev_ctx *, pgadev_pop *, int32_t *host_pairs);
  * population's device index list `slot` (0 = emigrants, 1 = victims).  Async. */
 void pgadev_select_top(pgadev_ctx *, pgadev_pop *, uint64_t k, int worst, int slot);
 void pgadev_download_top(pgadev_ctx *, pgadev_pop *, int slot, uint64_t k, uint32_t *host_idx);
+/* the scores of those k individuals, gathered on the device (k floats cross the bus) */
+void pgadev_download_top_scores(pgadev_ctx *, pgadev_pop *, int slot, uint64_t k, float *host_scores);
 /* size the outbox/inbox for k rows (allocates; call outside NCCL groups) */
 void pgadev_reserve_boxes(pgadev_ctx *, pgadev_pop *, uint64_t k);
 /* gather the k emigrants (rows + scores) listed in slot 0 into the outbox */

@@ -371,16 +371,16 @@ static unsigned top_of(pga_t *p, unsigned pi, unsigned length, struct ranked *ou
 	if (!pop->scores_valid)
 		evaluate_async(p, pop);
 	uint32_t *idx = (uint32_t *)malloc(sizeof(uint32_t) * length);
-	float *all = (float *)malloc(sizeof(float) * pop->size);
+	float *top = (float *)malloc(sizeof(float) * length);
 	pgadev_select_top(p->dev, pop->dev, length, 0, 0);
 	pgadev_download_top(p->dev, pop->dev, 0, length, idx);
-	pgadev_download_scores(p->dev, pop->dev, all);
+	pgadev_download_top_scores(p->dev, pop->dev, 0, length, top); /* `length` scores, not the whole array */
 	for (unsigned j = 0; j < length; ++j) {
-		out[j].key = order_key(all[idx[j]]);
+		out[j].key = order_key(top[j]);
 		out[j].pop = pi;
 		out[j].idx = idx[j];
 	}
-	free(all);
+	free(top);
 	free(idx);
 	qsort(out, length, sizeof(*out), ranked_cmp);
 	return length;
@@ -524,9 +524,18 @@ static void exchange_start(pga_t *p, struct exchange *ex, float pct)
 	p->migrate_round += 1;
 	memset(ex->k_in, 0, sizeof(ex->k_in));
 
-	/* boxes first: allocation must stay outside the NCCL group */
-	for (unsigned s = 0; s < K; ++s)
-		pgadev_reserve_boxes(p->dev, p->populations[s]->dev, pgax_migration_count(p->populations[s]->size, pct));
+	/* boxes first: allocation must stay outside the NCCL group.  An island's inbox takes
+	 * what its source sends, min(count(source), own size), which exceeds its own count
+	 * when the source is the larger island: size both boxes for the largest local sender */
+	uint64_t k_max = 0;
+	for (unsigned s = 0; s < K; ++s) {
+		uint64_t k = pgax_migration_count(p->populations[s]->size, pct);
+		if (k > k_max) k_max = k;
+	}
+	for (unsigned s = 0; s < K; ++s) {
+		uint64_t cap = p->populations[s]->size < k_max ? p->populations[s]->size : k_max;
+		pgadev_reserve_boxes(p->dev, p->populations[s]->dev, cap);
+	}
 
 	/* emigrants are ranked and packed on the side stream: they only read the
 	 * generation that just finished, so this overlaps the next generation */
@@ -821,5 +830,6 @@ int pgax_dist_world(pga_t *p) { return p->world; }
 
 float pgax_last_run_ms(pga_t *p) { return p->last_run_ms; }
 unsigned long long pgax_kernel_launches(pga_t *p) { return pgadev_ctx_launches(p->dev); }
+unsigned long long pgax_bytes_to_host(pga_t *p) { return pgadev_ctx_d2h_bytes(p->dev); }
 
 const char *pgax_version(void) { return "libpga-b200 0.1 (sm_100a)"; }

@@ -127,7 +127,13 @@ __global__ void __launch_bounds__(128) generation_hooks(const __grid_constant__ 
 
     uint32_t p1 = 0, p2 = 0;
     if (PH & PH_CROSSOVER) {
-        if (stage_parents && t == 0) mbar_arrive_expect_tx(bar, nact * 2u * row_bytes);
+        if (stage_parents && t == 0) {
+            // a crossover hook gets what the reference hands it (src/pga.cu:302): the child
+            // row starts as the row next_gen holds at that index (the generation before
+            // last), so a hook that leaves genes unwritten yields the same child here
+            mbar_arrive_expect_tx(bar, nact * 3u * row_bytes);
+            bulk_load(s_child, a.nxt + (size_t)base * S, nact * row_bytes, bar);
+        }
         if (active) {
             p1 = tournament(a.score_in, u0, u1, a.nf, a.n);  // src/pga.cu:306
             p2 = tournament(a.score_in, u2, u3, a.nf, a.n);  // src/pga.cu:307
@@ -1399,6 +1405,11 @@ __global__ void unpack_rows(uint32_t* rows, float* score, const uint32_t* __rest
         reinterpret_cast<uint4*>(rows)[(size_t)dst * nblk + b] = __ldg(reinterpret_cast<const uint4*>(box) + e);
         if (b == 0) score[dst] = box_score[j];
     }
+}
+
+__global__ void gather_scores(const float* __restrict__ score, const uint32_t* __restrict__ idx, uint32_t k, float* out)
+{
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < k; j += gridDim.x * blockDim.x) out[j] = score[idx[j]];
 }
 
 // host rows are unpadded; device rows are padded to a multiple of 4 words

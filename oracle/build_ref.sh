@@ -6,6 +6,9 @@
 #   oracle/_ref/dropin/test{1,2,3}  the SAME unmodified demo sources linked against
 #                                   THIS repository's libpga.a (the drop-in check)
 #   oracle/_ref/gen                 the reference's test3 instance generator
+#   oracle/_ref/pin/pin{1,2,3}      the reference library + its demo hooks, cuRAND replaced at
+#                                   link time by oracle/curand_shim.c, compared lock-step with
+#                                   the oracle (oracle/ref_pin.cu)
 # Only the architecture flag differs from the reference's Makefiles (-arch=sm_20 is
 # rejected by nvcc 12.9; Makefile:2, test/Makefile:2-3).  Outputs are git-ignored but
 # travel to the GPU box.  Test infrastructure, not product.
@@ -35,5 +38,23 @@ for t in test test2 test3; do
     i=$((i + 1))
 done
 /usr/bin/gcc -O2 -w -o "$OUT/gen" "$REF/test3/gen.c" 2>/dev/null || gcc -O2 -w -o "$OUT/gen" "$REF/test3/gen.c"
+
+# ---- the pin: the reference's own kernels against the oracle, bit for bit ----------------
+# oracle/_ref/pin/pinN = oracle/ref_pin.cu (-DPIN_CASE=N) + the reference's unmodified
+# test*/test.cu (main renamed, so its device hooks are the reference's own code) +
+# libpga_ref.a + oracle/curand_shim.c IN PLACE OF -lcurand + oracle/pga_oracle.c.
+HOSTCC=/usr/bin/gcc; [ -x $HOSTCC ] || HOSTCC=gcc
+CUDA_INC="$(dirname "$(dirname "$(command -v nvcc)")")/include"
+mkdir -p "$OUT/pin"
+$HOSTCC -O2 -ffp-contract=off -fopenmp -fPIC -c "$HERE/pga_oracle.c" -o "$OUT/obj/oracle.o"
+$HOSTCC -O2 -fopenmp -fPIC -I"$CUDA_INC" -I"$HERE" -c "$HERE/curand_shim.c" -o "$OUT/obj/shim.o"
+i=1
+for t in test test2 test3; do
+    nvcc -dc $ARCH -w -Dmain=reference_demo_main "$REF/$t/test.cu" -I"$REF/include" -o "$OUT/obj/${t}_hooks.o"
+    nvcc -dc $ARCH -w -DPIN_CASE=$i "$HERE/ref_pin.cu" -I"$REF/include" -I"$HERE" -o "$OUT/obj/pin$i.o"
+    nvcc $ARCH "$OUT/obj/pin$i.o" "$OUT/obj/${t}_hooks.o" "$OUT/obj/shim.o" "$OUT/obj/oracle.o" "$OUT/libpga_ref.a" \
+        -Xcompiler -fopenmp -lgomp -lm -o "$OUT/pin/pin$i"
+    i=$((i + 1))
+done
 rm -rf "$OUT/obj"
-ls -la "$OUT" "$OUT/ref" "$OUT/dropin"
+ls -la "$OUT" "$OUT/ref" "$OUT/dropin" "$OUT/pin"

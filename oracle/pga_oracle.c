@@ -852,8 +852,24 @@ void opga_demo_tsp_crossover(float *p1, float *p2, float *c, float *rnd, unsigne
 	}
 }
 
+/* test hooks without a counterpart in the reference's demos (see pga_demo_hooks.cu) */
+void opga_demo_even_crossover(float *p1, float *p2, float *c, float *rnd, unsigned len)
+{
+	for (unsigned k = 0; k < len; k += 2)
+		c[k] = rnd[k] > 0.5f ? p1[k] : p2[k];
+}
+
+void opga_demo_blend_mutate(float *g, float *rnd, unsigned len)
+{
+	for (unsigned k = 0; k < len; ++k)
+		if (rnd[k] < 0.125f)
+			g[k] = 0.5f * (g[k] + rnd[(k + 1) % len]);
+}
+
 void *opga_demo_hook(const char *name)
 {
+	if (!strcmp(name, "even_crossover")) return (void *)opga_demo_even_crossover;
+	if (!strcmp(name, "blend_mutate")) return (void *)opga_demo_blend_mutate;
 	if (!strcmp(name, "sum_obj")) return (void *)opga_demo_sum_obj;
 	if (!strcmp(name, "knapsack_obj")) return (void *)opga_demo_knapsack_obj;
 	if (!strcmp(name, "tsp_obj")) return (void *)opga_demo_tsp_obj;

@@ -118,6 +118,27 @@ def test_pga_migrate_random_exchange(pga, oracle):
         assert_islands_equal(gps, ops)
 
 
+@pytest.mark.parametrize("sizes", [(10000, 1000), (1000, 10000, 37), (64, 5000)])
+def test_islands_of_unequal_size(pga, oracle, sizes):
+    # pga.h gives every population its own size (include/pga.h:61-63).  An island receives
+    # min(count(source), own size) rows, which is more than its own "top pct" when the source
+    # is larger: 10000 -> 1000 at 10 % moves 1000 rows into an island whose own count is 100.
+    g = pga(23)
+    o = oracle.Oracle(23, threads=8)
+    gps = [g.create_population(n, 192, encoding=pg.GENES_BITS) for n in sizes]
+    ops = [o.create_population(n, 192, oracle.GENES_BITS) for n in sizes]
+    g.set_builtin_objective(pg.OBJ_ONEMAX); o.set_builtin_objective(oracle.OBJ_ONEMAX)
+    g.set_topology(pg.TOPO_RING); o.set_topology(oracle.TOPO_RING)
+    g.run_islands(2, 0, 0.0); o.run_islands(2, 0, 0.0)
+    g.migrate(10.0); o.migrate(10.0)
+    assert_islands_equal(gps, ops)
+    g.run_islands(9, 2, 10.0); o.run_islands(9, 2, 10.0)
+    assert_islands_equal(gps, ops)
+    g.migrate_between(gps[0], gps[1], 50.0); o.migrate_between(ops[0], ops[1], 50.0)
+    assert_islands_equal(gps, ops)
+    o.close()
+
+
 def test_migration_spreads_a_planted_optimum(pga):
     # size-independent property: with a ring and top-1% migration a planted perfect
     # individual reaches every island
@@ -145,6 +166,25 @@ def test_best_queries_match_oracle(pga, oracle):
     all_g = g.get_best_top_all(5)
     all_o = o.get_best_top_all(5)
     assert len(all_g) == 5 and all(same_bits(a, b) for a, b in zip(all_g, all_o))
+
+
+def test_get_best_top_moves_only_the_listed_scores(pga, oracle):
+    # the `length` best of 2^22 individuals: the ranking, the score look-up and the row
+    # gather all happen on the device; a few KB cross the bus, not the 16 MiB score array
+    n = 1 << 22
+    g = pga(4)
+    p = g.create_population(n, 8)
+    g.set_builtin_objective(pg.OBJ_SUM)
+    g.run(1)
+    scores = p.scores()
+    before = g.bytes_to_host
+    rows = g.get_best_top(p, 7)
+    moved = g.bytes_to_host - before
+    assert moved < 64 * 1024, moved
+    want = oracle.select_top(scores, 7)
+    order = sorted(want, key=lambda i: (-scores[i], i))
+    genes = p.genes()
+    assert len(rows) == 7 and all(same_bits(r, genes[i]) for r, i in zip(rows, order))
 
 
 def test_evaluate_all_and_friends(pga, oracle):

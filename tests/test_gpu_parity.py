@@ -282,6 +282,42 @@ def test_builtin_objective_with_hook_crossover(pga, oracle, tsp_matrix):
     o.close()
 
 
+@pytest.mark.parametrize("size,length", [(2000, 100), (333, 37), (5000, 10)])
+def test_crossover_hook_that_leaves_genes_unwritten(pga, oracle, size, length):
+    # src/pga.cu:302: the child row handed to the crossover hook starts as the row next_gen
+    # holds at that index; a hook that writes only the even genes leaves the odd ones as they
+    # were two generations ago (zero in the first generation: the buffer starts zeroed here
+    # and in the oracle, where the reference leaves cudaMalloc's contents)
+    g, o, gp, op = setup_pair(pga, oracle, 6, size, length, obj="sum_obj", xover="even_crossover")
+    for gen in range(6):
+        g.run(1); o.run(1)
+        assert same_bits(gp.genes(), op.genes()), gen
+        assert same_bits(gp.scores(), op.scores()), gen
+    # stepwise too: crossover alone, then mutate alone
+    g.fill_random_values(gp); o.fill_random_values(op)
+    g.crossover(gp); o.crossover(op)
+    assert same_bits(gp.next_genes(), op.next_genes())
+    g.mutate(gp); o.mutate(op)
+    assert same_bits(gp.next_genes(), op.next_genes())
+    o.close()
+
+
+@pytest.mark.parametrize("xover", [None, "tsp_crossover"])
+def test_mutate_hook_reads_its_rand_row(pga, oracle, tsp_matrix, xover):
+    # include/pga.h:47, :71-77: a user mutation gets the genome and that individual's rand row
+    g, o, gp, op = setup_pair(pga, oracle, 12, 1500, 100, obj="sum_obj", xover=xover)
+    g.tsp_load(tsp_matrix); o.tsp_load(tsp_matrix)
+    g.set_mutate_function("blend_mutate"); o.set_mutate_hook("blend_mutate")
+    for gen in range(5):
+        g.run(1); o.run(1)
+        assert same_bits(gp.genes(), op.genes()), gen
+        assert same_bits(gp.scores(), op.scores()), gen
+    g.set_mutate_function(None); o.set_mutate_hook(None)   # NULL restores the default (include/pga.h:76)
+    g.run(2); o.run(2)
+    assert same_bits(gp.genes(), op.genes())
+    o.close()
+
+
 # ---- API behaviour -------------------------------------------------------------------
 
 def test_create_population_limits(pga):
