@@ -30,6 +30,7 @@ extern "C" {
 #define PGAX_ENOSYS (-3)   /* combination not supported (e.g. hooks on packed bits) */
 #define PGAX_ENCCL (-4)    /* NCCL library not loadable */
 #define PGAX_ECUDA (-5)    /* a CUDA call failed (only from entry points that say so) */
+#define PGAX_EIO (-6)      /* a file could not be read or written */
 
 enum pgax_gene_encoding {
 	PGAX_GENES_F32 = 0, /* libpga's `gene`: one float per gene */
@@ -66,6 +67,50 @@ population_t *pgax_create_population(pga_t *, unsigned long size, unsigned genom
  * PGAX_OBJ_HOOK, returns to the user hook. */
 int pgax_set_builtin_objective(pga_t *, enum pgax_objective which);
 
+/* ---- selection schemes -----------------------------------------------------
+ * The reference declares enum crossover_selection_type as "pretty much just a
+ * placeholder" with the single member TOURNAMENT, notes "XXX add different types of
+ * selections" (include/pga.h:36-42, :103) and ignores the argument of pga_crossover
+ * (src/pga.cu:319, :329).  pga.h stays frozen, so the further schemes are values of the
+ * same enum type defined here:
+ *   TOURNAMENT              the reference's tournament of TOURNAMENT_POPULATION = 2
+ *                           candidates (src/pga.cu:278-292)
+ *   PGAX_TOURNAMENT_OF(k)   the same rule among k candidates, 1 <= k <= PGAX_MAX_TOURNAMENT:
+ *                           parent 1 from draws 0..k-1 of the child's rand row, parent 2
+ *                           from draws k..2k-1; a later candidate wins only if strictly
+ *                           better.  k = 1 is uniform selection (no pressure).
+ * pga_crossover / pga_crossover_all honour their type argument (an unknown value ends the
+ * program with a message, it is not ignored); pga_run and pga_run_islands use the scheme
+ * set here (default TOURNAMENT, as src/pga.cu:384 passes). */
+#define PGAX_SELECTION_BASE 0x100u
+#define PGAX_MAX_TOURNAMENT 16u
+#define PGAX_TOURNAMENT_OF(k) ((enum crossover_selection_type)(PGAX_SELECTION_BASE + (unsigned)(k)))
+#define PGAX_SELECT_UNIFORM PGAX_TOURNAMENT_OF(1)
+int pgax_set_selection(pga_t *, enum crossover_selection_type);
+
+/* ---- early stop ----------------------------------------------------------------
+ * include/pga.h:141 and :147 promise that pga_run / pga_run_islands run "until
+ * n-generations or obj_func(best_genome) == value"; no signature carries the value and
+ * the reference has no such code.  pgax_set_target(value, check_every) arms it: the run
+ * ends after the first generation g, g a multiple of check_every, in which the best
+ * score of the population (of any island, on any rank) is >= value.  The check costs one
+ * 4-byte copy that overlaps the next generation; that next generation is dropped when
+ * the check succeeds.  check_every = 0 disarms.  pgax_generations_run tells how many
+ * generations the last pga_run / pga_run_islands executed. */
+int pgax_set_target(pga_t *, float value, unsigned check_every);
+unsigned pgax_generations_run(pga_t *);
+
+/* ---- dump / restore --------------------------------------------------------------
+ * The reference has no checkpointing.  pgax_save writes the solver's seed, island
+ * schedule state and, per population, shape, epoch, current generation and scores to
+ * `path`; pgax_restore reads them back into a solver that is empty (the populations
+ * are created) or holds populations of the same shapes.  A run resumed from the file
+ * continues exactly as the uninterrupted run would.  Hooks are device addresses of the
+ * running process and are not saved: set them again after a restore.  next_gen is not
+ * saved (it only matters to a crossover hook that leaves genes unwritten). */
+int pgax_save(pga_t *, const char *path);
+int pgax_restore(pga_t *, const char *path);
+
 /* Suppresses the "%f\n" line pga_get_best prints (src/pga.cu:230). */
 int pgax_set_quiet(pga_t *, int quiet);
 
@@ -81,6 +126,8 @@ int pgax_capture_selection(pga_t *, population_t *, int enable);
 
 /* Row layout on the host: [size][row_words] 32-bit words, row_words =
  * genome_len (f32) or ceil(genome_len/32) (bits); no padding. */
+population_t *pgax_population(pga_t *, unsigned index); /* the index-th population, NULL past the end */
+int pgax_encoding(population_t *);                       /* enum pgax_gene_encoding */
 unsigned pgax_row_words(population_t *);
 unsigned long pgax_population_size(population_t *);
 unsigned pgax_genome_len(population_t *);

@@ -44,8 +44,15 @@ SIGNATURES = {
     "pgax_create_population": (_vp, [_vp, _ul, _ui, _i32]),
     "pgax_set_builtin_objective": (_i32, [_vp, _i32]),
     "pgax_set_quiet": (_i32, [_vp, _i32]),
+    "pgax_set_selection": (_i32, [_vp, _i32]),
+    "pgax_set_target": (_i32, [_vp, _f32, _ui]),
+    "pgax_generations_run": (_ui, [_vp]),
+    "pgax_save": (_i32, [_vp, C.c_char_p]),
+    "pgax_restore": (_i32, [_vp, C.c_char_p]),
     "pgax_set_stream": (_i32, [_vp, _vp]),
     "pgax_capture_selection": (_i32, [_vp, _vp, _i32]),
+    "pgax_population": (_vp, [_vp, _ui]),
+    "pgax_encoding": (_i32, [_vp]),
     "pgax_row_words": (_ui, [_vp]),
     "pgax_population_size": (_ul, [_vp]),
     "pgax_genome_len": (_ui, [_vp]),

@@ -16,6 +16,13 @@ RANDOM_POPULATION = 0   # enum population_type (include/pga.h:31-34)
 TOURNAMENT = 0          # enum crossover_selection_type (include/pga.h:39-42)
 MAX_POPULATIONS = 10    # include/pga.h:44
 
+
+
+def tournament_of(k):
+    """PGAX_TOURNAMENT_OF(k): tournament among k candidates as a crossover_selection_type."""
+    return 0x100 + int(k)
+
+
 GENES_F32, GENES_BITS = 0, 1
 OBJ_HOOK, OBJ_SUM, OBJ_RASTRIGIN, OBJ_SPHERE, OBJ_ONEMAX = 0, 1, 2, 3, 4
 TOPO_RING, TOPO_RANDOM = 0, 1
@@ -151,6 +158,37 @@ class PGA:
     def set_builtin_objective(self, which):
         rc = self.L.pgax_set_builtin_objective(self.h, which)
         assert rc == 0, rc
+
+    def set_selection(self, type):
+        rc = self.L.pgax_set_selection(self.h, type)
+        assert rc == 0, rc
+
+    def set_target(self, value, check_every=1):
+        self.L.pgax_set_target(self.h, value, check_every)
+
+    @property
+    def generations_run(self):
+        return int(self.L.pgax_generations_run(self.h))
+
+    def save(self, path):
+        rc = self.L.pgax_save(self.h, str(path).encode())
+        if rc != 0:
+            raise OSError(f"pgax_save failed: {rc}")
+
+    def restore(self, path):
+        rc = self.L.pgax_restore(self.h, str(path).encode())
+        if rc != 0:
+            raise OSError(f"pgax_restore failed: {rc}")
+        if not self.pops:  # populations created by the restore: wrap them
+            i = 0
+            while True:
+                h = self.L.pgax_population(self.h, i)
+                if not h:
+                    break
+                enc = self.L.pgax_encoding(h)
+                self.pops.append(Population(self, h, enc))
+                i += 1
+        return self.pops
 
     def set_stream(self, cuda_stream):
         self.L.pgax_set_stream(self.h, cuda_stream)

@@ -53,6 +53,10 @@ struct pgadev_ctx {
     int no_hook_split;            // $PGA_NO_HOOK_SPLIT=1: generations with hooks are always one launch
     int no_coop;                  // $PGA_NO_COOP=1: rank with the 5-launch select instead of the cooperative kernel
     uint32_t reserve_now;         // SMs' worth of blocks the current launch leaves free (pgadev_step.reserve_sms)
+    // early-stop check (pgax_set_target): best score of the local populations
+    float* check_dev;
+    float* check_host;  // pinned
+    cudaEvent_t ev_check;
     int l2_persist;               // $PGA_L2_PERSIST: 1 = children being written persist in L2, 2 = the parents' buffer does (experiment)
     size_t l2_window_max;
 };
@@ -134,6 +138,7 @@ extern "C" pgadev_ctx* pgadev_ctx_create(void)
     CCE(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
     CCE(cudaEventCreate(&c->t0));
     CCE(cudaEventCreate(&c->t1));
+    CCE(cudaEventCreateWithFlags(&c->ev_check, cudaEventDisableTiming));
     const char* ht = getenv("PGA_HOOK_THREADS");
     c->hook_threads = ht ? atoi(ht) : 0;
     const char* e;
@@ -164,6 +169,9 @@ extern "C" void pgadev_ctx_destroy(pgadev_ctx* c)
     CCE(cudaEventDestroy(c->ev_packed));
     CCE(cudaEventDestroy(c->t0));
     CCE(cudaEventDestroy(c->t1));
+    CCE(cudaEventDestroy(c->ev_check));
+    if (c->check_dev) CCE(cudaFree(c->check_dev));
+    if (c->check_host) CCE(cudaFreeHost(c->check_host));
     CCE(cudaStreamDestroy(c->own_stream));
     CCE(cudaStreamDestroy(c->side));
     free(c);
@@ -495,7 +503,7 @@ static int launch_tiled(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 template <int ENC, int OBJ>
 static int launch_fast_ph(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a, uint32_t ph)
 {
-    if (ph == PH_FUSED) {
+    if (ph == PH_FUSED && a.tk == 2u) {  // the compile-time tilings are built for the reference's size-2 tournament
         int rc = launch_staged<ENC, OBJ>(c, p, a);
         if (rc <= 0) return rc;
         rc = launch_tiled<ENC, OBJ>(c, p, a);
@@ -533,6 +541,7 @@ extern "C" int pgadev_launch(pgadev_ctx* c, pgadev_pop* p, const pgadev_step* st
     a.lenf = (float)p->len;
     a.stride = p->stride;
     a.group = p->group;
+    a.tk = st->tournament ? st->tournament : 2u;
     a.draw = make_draw(st->seed, st->island, st->epoch);
     a.objective = st->objective;
     a.obj = (obj_fn)st->obj_hook;
@@ -876,6 +885,7 @@ struct nccl_api {
     ncclResult_t (*CommDestroy)(ncclComm_t);
     ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
     ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
     ncclResult_t (*GroupStart)(void);
     ncclResult_t (*GroupEnd)(void);
     const char* (*GetErrorString)(ncclResult_t);
@@ -898,6 +908,7 @@ static int nccl_load(void)
     SYM(CommDestroy, "ncclCommDestroy")
     SYM(Send, "ncclSend")
     SYM(Recv, "ncclRecv")
+    SYM(AllReduce, "ncclAllReduce")
     SYM(GroupStart, "ncclGroupStart")
     SYM(GroupEnd, "ncclGroupEnd")
     SYM(GetErrorString, "ncclGetErrorString")
@@ -955,6 +966,45 @@ extern "C" void pgadev_nccl_send_outbox(pgadev_ctx* c, pgadev_pop* src, uint64_t
 extern "C" void pgadev_nccl_recv_inbox(pgadev_ctx* c, pgadev_pop* dst, uint64_t k, int peer)
 {
     NCE(g_nccl.Recv(dst->inbox, box_words(dst, k), ncclUint32, peer, c->comm, c->side));
+}
+
+// ---- early stop: best score of all local populations, read back without stalling ------------------
+// The generation kernel already reduced each population's best into its ring slot; one
+// small launch turns the slots into a float, an optional all-reduce takes the maximum over
+// the ranks, and 4 bytes travel to pinned host memory behind an event.  The host looks at
+// them one generation later (pgadev_check_wait), so the copy overlaps the next generation.
+extern "C" void pgadev_check_begin(pgadev_ctx* c, pgadev_pop** pops, const int* reduced_in_kernel, unsigned count, int all_ranks)
+{
+    use_device(c);
+    if (!c->check_dev) {
+        CCE(cudaMalloc((void**)&c->check_dev, sizeof(float)));
+        CCE(cudaMallocHost((void**)&c->check_host, sizeof(float)));
+    }
+    BestSlots slots;
+    memset(&slots, 0, sizeof(slots));
+    for (unsigned i = 0; i < count && i < 10u; ++i) {
+        pgadev_pop* p = pops[i];
+        if (p->n == 0) continue;
+        if (!reduced_in_kernel[i]) {
+            const uint32_t grid = grid_for(p->n, 256 * 8, (uint32_t)c->sm_count * 8u);
+            reduce_best<<<grid, 256, 0, c->stream>>>(p->score[p->sidx], (uint32_t)p->n, p->best, p->best_seq & 3u);
+            LAUNCH_CHECK(c);
+            p->best_seq += 1;
+        }
+        slots.slot[slots.count++] = p->best + ((p->best_seq - 1u) & 3u);
+    }
+    best_of_slots<<<1, 32, 0, c->stream>>>(slots, c->check_dev);
+    LAUNCH_CHECK(c);
+    if (all_ranks && c->comm) NCE(g_nccl.AllReduce(c->check_dev, c->check_dev, 1, ncclFloat, ncclMax, c->comm, c->stream));
+    CCE(cudaMemcpyAsync(c->check_host, c->check_dev, sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    c->d2h_bytes += sizeof(float);
+    CCE(cudaEventRecord(c->ev_check, c->stream));
+}
+
+extern "C" float pgadev_check_wait(pgadev_ctx* c)
+{
+    CCE(cudaEventSynchronize(c->ev_check));
+    return *c->check_host;
 }
 
 // ---- ranking without any allocation ----------------------------------------------------------------

@@ -38,6 +38,7 @@ typedef struct pgadev_step {
 	void *mutate_hook;
 	void *crossover_hook;
 	uint32_t reserve_sms; /* leave this many SMs' worth of blocks unlaunched, for work on the side stream */
+	uint32_t tournament;  /* candidates per parent in the selection; 2 = the reference's TOURNAMENT */
 } pgadev_step;
 
 pgadev_ctx *pgadev_ctx_create(void);
@@ -68,6 +69,13 @@ void pgadev_swap_scores(pgadev_pop *); /* shadow scores become score[] */
 /* first maximum of score[] (reference tie rule), from the in-kernel reduction when
  * `reduced_in_kernel`, else from a reduction pass.  Blocking. */
 void pgadev_best(pgadev_ctx *, pgadev_pop *, int reduced_in_kernel, uint64_t *index, float *score);
+
+/* Early-stop check.  begin: the maximum best score over `count` local populations (and over
+ * all ranks when all_ranks), queued on the main stream behind the launches so far, 4 bytes
+ * to pinned host memory.  reduced_in_kernel[i] says whether population i's best slot is
+ * current; if not a reduction pass runs first.  wait: blocks until that copy landed. */
+void pgadev_check_begin(pgadev_ctx *, pgadev_pop **pops, const int *reduced_in_kernel, unsigned count, int all_ranks);
+float pgadev_check_wait(pgadev_ctx *);
 
 /* blocking copies between host rows (unpadded) and device rows (padded) */
 void pgadev_upload_rows(pgadev_ctx *, pgadev_pop *, const void *host, int next_gen);

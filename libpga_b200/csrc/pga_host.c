@@ -48,6 +48,11 @@ struct pga { /* reference: src/pga.cu:48-56 */
 	unsigned reserve_sms;   /* blocks held back in the next launches (an exchange is in flight beside them) */
 	unsigned reserve_conf;  /* $PGA_RESERVE_SMS, default 8 */
 	float last_run_ms;
+	unsigned tournament;      /* candidates per parent used by pga_run / pga_run_islands; 2 = TOURNAMENT */
+	int target_armed;         /* pgax_set_target: stop when the best score reaches target_value */
+	float target_value;
+	unsigned target_every;
+	unsigned generations_run; /* by the last pga_run / pga_run_islands */
 	pgadev_ctx *dev;
 };
 
@@ -72,6 +77,7 @@ pga_t *pga_init() /* src/pga.cu:148-164 */
 	p->builtin = PGAX_OBJ_HOOK;
 	p->topology = PGAX_TOPO_RANDOM; /* "random migrations", include/pga.h:148 */
 	p->delay = 1;
+	p->tournament = 2; /* TOURNAMENT_POPULATION, src/pga.cu:278 */
 	env = getenv("PGA_RESERVE_SMS");
 	p->reserve_conf = env && *env ? (unsigned)strtoul(env, NULL, 0) : 8u;
 	p->rank = 0;
@@ -163,6 +169,7 @@ static void fill_step(pga_t *p, population_t *pop, unsigned phases, pgadev_step 
 	st->mutate_hook = (void *)p->mutate;
 	st->crossover_hook = (void *)p->crossover;
 	st->reserve_sms = p->reserve_sms;
+	st->tournament = p->tournament;
 	if ((phases & PGADEV_PH_EVALUATE) && p->builtin == PGAX_OBJ_HOOK && p->objective == NULL)
 		die("no objective function set (pga_set_objective_function)");
 }
@@ -215,19 +222,51 @@ void pga_evaluate_all(pga_t *p) /* src/pga.cu:272-276 */
 	pgadev_ctx_sync(p->dev);
 }
 
+/* Candidates per parent a selection type stands for, 0 if it is not a selection type.
+ * The reference declares the enum as "pretty much just a placeholder" and drops the
+ * argument (include/pga.h:36-42, :103 "XXX add different types of selections";
+ * src/pga.cu:319, :329).  Here TOURNAMENT is the reference's size-2 tournament and
+ * PGAX_TOURNAMENT_OF(k) a tournament among k candidates (k = 1: uniform selection). */
+static unsigned selection_size(enum crossover_selection_type type)
+{
+	if (type == TOURNAMENT)
+		return 2;
+	unsigned v = (unsigned)type;
+	if (v > PGAX_SELECTION_BASE && v <= PGAX_SELECTION_BASE + PGAX_MAX_TOURNAMENT)
+		return v - PGAX_SELECTION_BASE;
+	return 0;
+}
+
+static void crossover_with(pga_t *p, population_t *pop, enum crossover_selection_type type)
+{
+	unsigned k = selection_size(type), keep = p->tournament;
+	if (k == 0)
+		die("pga_crossover: unknown selection type");
+	p->tournament = k;
+	launch(p, pop, PGADEV_PH_CROSSOVER);
+	p->tournament = keep;
+}
+
 void pga_crossover(pga_t *p, population_t *pop, enum crossover_selection_type type) /* src/pga.cu:319-325 */
 {
-	(void)type; /* ignored by the reference too */
-	launch(p, pop, PGADEV_PH_CROSSOVER);
+	crossover_with(p, pop, type);
 	pgadev_ctx_sync(p->dev);
 }
 
 void pga_crossover_all(pga_t *p, enum crossover_selection_type type) /* src/pga.cu:327-331 */
 {
-	(void)type;
 	for (unsigned i = 0; i < p->p_count; ++i)
-		launch(p, p->populations[i], PGADEV_PH_CROSSOVER);
+		crossover_with(p, p->populations[i], type);
 	pgadev_ctx_sync(p->dev);
+}
+
+int pgax_set_selection(pga_t *p, enum crossover_selection_type type)
+{
+	unsigned k = selection_size(type);
+	if (k == 0)
+		return PGAX_EINVAL;
+	p->tournament = k;
+	return 0;
 }
 
 void pga_mutate(pga_t *p, population_t *pop) /* src/pga.cu:349-354 */
@@ -257,6 +296,47 @@ void pga_fill_random_values(pga_t *p, population_t *pop) /* src/pga.cu:103-105 *
 	pop->epoch += 1; /* counter-based draws: a new epoch IS a new rand buffer */
 }
 
+/* ---- early stop -----------------------------------------------------------------
+ * include/pga.h:141 and :147 say pga_run / pga_run_islands run "until n-generations or
+ * obj_func(best_genome) == value"; no signature carries the value and the reference has
+ * no such code.  pgax_set_target arms it: after every generation g that is a multiple of
+ * `every`, the best score of the population(s) -- already reduced inside the generation
+ * kernel -- is copied to the host (8 bytes) while generation g+1 runs; if it had reached
+ * the target, generation g+1 is dropped (the two buffers are swapped back) and the run
+ * ends with generation g current.  Nothing is launched or copied when no target is set. */
+static int target_check_due(pga_t *p, unsigned g, unsigned n)
+{
+	return p->target_armed && p->target_every && g % p->target_every == 0 && g < n;
+}
+
+static void target_check_begin(pga_t *p, unsigned count)
+{
+	pgadev_pop *pops[MAX_POPULATIONS];
+	int reduced[MAX_POPULATIONS];
+	for (unsigned s = 0; s < count; ++s) {
+		pops[s] = p->populations[s]->dev;
+		reduced[s] = p->populations[s]->best_in_kernel || p->populations[s]->size == 0;
+		p->populations[s]->best_in_kernel = 1;
+	}
+	pgadev_check_begin(p->dev, pops, reduced, count, p->world > 1 && p->have_comm);
+}
+
+static int target_reached(pga_t *p)
+{
+	float best = pgadev_check_wait(p->dev);
+	return best >= p->target_value;
+}
+
+/* drop the generation that was launched speculatively: the previous one is current again */
+static void undo_generation(population_t *pop)
+{
+	pgadev_swap_genes(pop->dev);
+	pgadev_swap_scores(pop->dev);
+	pop->epoch -= 1;
+	pop->scores_valid = 1;
+	pop->best_in_kernel = 0; /* the best slot of the dropped launch is stale: reduce again when asked */
+}
+
 void pga_run(pga_t *p, unsigned n) /* src/pga.cu:376-391 */
 {
 	if (p->p_count == 0)
@@ -265,8 +345,23 @@ void pga_run(pga_t *p, unsigned n) /* src/pga.cu:376-391 */
 	if (!pop->scores_valid)
 		evaluate_async(p, pop);
 	pgadev_timer_start(p->dev);
-	for (unsigned i = 0; i < n; ++i)
+	unsigned done = n;
+	int pending = 0;
+	for (unsigned g = 1; g <= n; ++g) {
 		generation_async(p, pop);
+		/* the check of generation g-1 was read back while generation g ran */
+		if (pending && target_reached(p)) {
+			undo_generation(pop);
+			done = g - 1;
+			break;
+		}
+		pending = 0;
+		if (target_check_due(p, g, n)) {
+			target_check_begin(p, 1); /* pga_run works on populations[0] only (src/pga.cu:382-386) */
+			pending = 1;
+		}
+	}
+	p->generations_run = done;
 	pgadev_timer_stop(p->dev);
 	p->last_run_ms = pgadev_timer_ms(p->dev);
 	pgadev_ctx_sync(p->dev);
@@ -662,6 +757,8 @@ void pga_run_islands(pga_t *p, unsigned n, unsigned m, float pct) /* stub: src/p
 	unsigned total = p->p_count * (unsigned)p->world;
 	ensure_scores(p);
 	pgadev_timer_start(p->dev);
+	unsigned done = n;
+	int pending = 0;
 	for (unsigned g = 1; g <= n; ++g) {
 		/* generation start+2 overwrites the buffers the emigrants are packed from */
 		if (ex.active && g == ex.start_gen + 2)
@@ -672,6 +769,14 @@ void pga_run_islands(pga_t *p, unsigned n, unsigned m, float pct) /* stub: src/p
 		for (unsigned s = 0; s < p->p_count; ++s)
 			generation_async(p, p->populations[s]);
 		p->reserve_sms = 0;
+		if (pending && target_reached(p)) { /* include/pga.h:147; see pga_run */
+			for (unsigned s = 0; s < p->p_count; ++s)
+				undo_generation(p->populations[s]);
+			done = g - 1;
+			ex.active = 0; /* an exchange still in flight never lands */
+			break;
+		}
+		pending = 0;
 		if (ex.active && ex.land_gen == g)
 			exchange_finish(p, &ex);
 		if (m && g % m == 0 && g + p->delay <= n && total > 1 && !ex.active) {
@@ -681,7 +786,12 @@ void pga_run_islands(pga_t *p, unsigned n, unsigned m, float pct) /* stub: src/p
 			if (p->delay == 0)
 				exchange_finish(p, &ex);
 		}
+		if (target_check_due(p, g, n)) {
+			target_check_begin(p, p->p_count);
+			pending = 1;
+		}
 	}
+	p->generations_run = done;
 	pgadev_timer_stop(p->dev);
 	p->last_run_ms = pgadev_timer_ms(p->dev);
 	pgadev_ctx_sync(p->dev);
@@ -710,6 +820,8 @@ int pgax_capture_selection(pga_t *p, population_t *pop, int enable)
 	return 0;
 }
 
+population_t *pgax_population(pga_t *p, unsigned index) { return index < p->p_count ? p->populations[index] : NULL; }
+int pgax_encoding(population_t *pop) { return pop->encoding; }
 unsigned pgax_row_words(population_t *pop) { return pgadev_pop_row_words(pop->dev); }
 unsigned long pgax_population_size(population_t *pop) { return pop->size; }
 unsigned pgax_genome_len(population_t *pop) { return pop->genome_len; }
@@ -786,6 +898,158 @@ int pgax_select_top(pga_t *p, population_t *pop, unsigned long k, int worst, uin
 	pgadev_select_top(p->dev, pop->dev, k, worst ? 1 : 0, worst ? 1 : 0);
 	pgadev_download_top(p->dev, pop->dev, worst ? 1 : 0, k, host_indices);
 	return 0;
+}
+
+int pgax_set_target(pga_t *p, float value, unsigned check_every)
+{
+	p->target_armed = check_every != 0;
+	p->target_value = value;
+	p->target_every = check_every;
+	return 0;
+}
+
+unsigned pgax_generations_run(pga_t *p) { return p->generations_run; }
+
+/* ---- dump / restore (the reference has no checkpointing) ---- */
+#define PGAX_FILE_MAGIC "PGAB200"
+#define PGAX_FILE_VERSION 1u
+
+struct file_header {
+	char magic[8];
+	uint32_t version, p_count;
+	uint64_t seed;
+	uint32_t migrate_round, delay;
+	int32_t topology, builtin;
+	uint32_t tournament, pad;
+};
+
+struct file_pop {
+	uint64_t size;
+	uint32_t genome_len, row_words, island, epoch;
+	int32_t encoding, scores_valid;
+};
+
+int pgax_save(pga_t *p, const char *path)
+{
+	if (path == NULL)
+		return PGAX_EINVAL;
+	pgadev_ctx_sync(p->dev);
+	FILE *f = fopen(path, "wb");
+	if (f == NULL)
+		return PGAX_EIO;
+	struct file_header h;
+	memset(&h, 0, sizeof(h));
+	memcpy(h.magic, PGAX_FILE_MAGIC, 8);
+	h.version = PGAX_FILE_VERSION;
+	h.p_count = p->p_count;
+	h.seed = p->seed;
+	h.migrate_round = p->migrate_round;
+	h.delay = p->delay;
+	h.topology = p->topology;
+	h.builtin = p->builtin;
+	h.tournament = p->tournament;
+	int ok = fwrite(&h, sizeof(h), 1, f) == 1;
+	for (unsigned i = 0; ok && i < p->p_count; ++i) {
+		population_t *pop = p->populations[i];
+		struct file_pop fp;
+		memset(&fp, 0, sizeof(fp));
+		fp.size = pop->size;
+		fp.genome_len = pop->genome_len;
+		fp.row_words = pgadev_pop_row_words(pop->dev);
+		fp.island = pop->island;
+		fp.epoch = pop->epoch;
+		fp.encoding = pop->encoding;
+		fp.scores_valid = pop->scores_valid;
+		ok = fwrite(&fp, sizeof(fp), 1, f) == 1;
+		size_t bytes = rows_bytes(pop);
+		void *rows = malloc(bytes ? bytes : 1);
+		float *scores = (float *)malloc(sizeof(float) * (pop->size ? pop->size : 1));
+		if (rows == NULL || scores == NULL) {
+			free(rows); free(scores);
+			ok = 0;
+			break;
+		}
+		if (pop->size) {
+			pgadev_download_rows(p->dev, pop->dev, rows, 0);
+			pgadev_download_scores(p->dev, pop->dev, scores);
+		}
+		ok = ok && fwrite(rows, 1, bytes, f) == bytes && fwrite(scores, sizeof(float), pop->size, f) == pop->size;
+		free(rows);
+		free(scores);
+	}
+	if (fclose(f) != 0)
+		ok = 0;
+	return ok ? 0 : PGAX_EIO;
+}
+
+int pgax_restore(pga_t *p, const char *path)
+{
+	if (path == NULL)
+		return PGAX_EINVAL;
+	FILE *f = fopen(path, "rb");
+	if (f == NULL)
+		return PGAX_EIO;
+	struct file_header h;
+	int rc = PGAX_EIO;
+	if (fread(&h, sizeof(h), 1, f) != 1 || memcmp(h.magic, PGAX_FILE_MAGIC, 8) != 0 || h.version != PGAX_FILE_VERSION ||
+	    h.p_count > MAX_POPULATIONS)
+		goto out;
+	if (p->p_count != 0 && p->p_count != h.p_count) {
+		rc = PGAX_EINVAL;
+		goto out;
+	}
+	int create = p->p_count == 0;
+	pgadev_ctx_sync(p->dev);
+	p->seed = h.seed;
+	p->migrate_round = h.migrate_round;
+	p->delay = h.delay;
+	p->topology = h.topology;
+	p->builtin = h.builtin;
+	p->tournament = h.tournament ? h.tournament : 2;
+	for (unsigned i = 0; i < h.p_count; ++i) {
+		struct file_pop fp;
+		if (fread(&fp, sizeof(fp), 1, f) != 1)
+			goto out;
+		population_t *pop;
+		if (create) {
+			pop = pgax_create_population(p, (unsigned long)fp.size, fp.genome_len, (enum pgax_gene_encoding)fp.encoding);
+			if (pop == NULL) {
+				rc = PGAX_EINVAL;
+				goto out;
+			}
+		} else {
+			pop = p->populations[i];
+			if (pop->size != fp.size || pop->genome_len != fp.genome_len || pop->encoding != fp.encoding) {
+				rc = PGAX_EINVAL;
+				goto out;
+			}
+		}
+		if (pgadev_pop_row_words(pop->dev) != fp.row_words) {
+			rc = PGAX_EINVAL;
+			goto out;
+		}
+		pop->island = fp.island;
+		pop->epoch = fp.epoch;
+		size_t bytes = rows_bytes(pop);
+		void *rows = malloc(bytes ? bytes : 1);
+		float *scores = (float *)malloc(sizeof(float) * (pop->size ? pop->size : 1));
+		int ok = rows != NULL && scores != NULL && fread(rows, 1, bytes, f) == bytes &&
+			 fread(scores, sizeof(float), pop->size, f) == pop->size;
+		if (ok && pop->size) {
+			pgadev_upload_rows(p->dev, pop->dev, rows, 0);
+			pgadev_upload_scores(p->dev, pop->dev, scores);
+		}
+		free(rows);
+		free(scores);
+		if (!ok)
+			goto out;
+		pop->scores_valid = fp.scores_valid;
+		pop->best_in_kernel = 0;
+	}
+	rc = 0;
+out:
+	fclose(f);
+	return rc;
 }
 
 int pgax_set_topology(pga_t *p, enum pgax_topology t)

@@ -44,6 +44,7 @@ struct GenArgs {
     float lenf;      // (float)len
     uint32_t stride; // 32-bit words per stored row, multiple of 4
     uint32_t group;  // fast path: lanes per child (power of two <= 32)
+    uint32_t tk;     // tournament size (candidates per parent); 2 = the reference's TOURNAMENT
     DrawCtx draw;
     int objective;
     obj_fn obj;
@@ -60,6 +61,27 @@ __device__ __forceinline__ uint32_t tournament(const float* __restrict__ score, 
     const uint32_t a = draw_index(ua, nf, n), b = draw_index(ub, nf, n);
     const float sa = __ldg(score + a), sb = __ldg(score + b);
     return sa < sb ? b : a;
+}
+
+// Tournament of K candidates on draws first .. first+K-1 of the child's rand row:
+// src/pga.cu:280-292 with TOURNAMENT_POPULATION = K (a later candidate wins only if
+// strictly better than the best so far).  The reference hard-wires K = 2; other sizes are
+// the selection schemes of include/pga_b200.h (PGAX_TOURNAMENT_OF).
+__device__ __forceinline__ uint32_t tournament_of(const DrawCtx& d, const float* __restrict__ score, uint32_t child, uint32_t first,
+                                                  uint32_t K, float nf, uint32_t n)
+{
+    uint32_t best = 0, have = 0xFFFFFFFFu;
+    float sbest = 0.f;
+    uint4 w = make_uint4(0, 0, 0, 0);
+    for (uint32_t i = 0; i < K; ++i) {
+        const uint32_t j = first + i;
+        if ((j >> 2) != have) { have = j >> 2; w = draw_block(d, STREAM_ROW, child, have); }
+        const uint32_t x = (j & 3u) == 0 ? w.x : (j & 3u) == 1 ? w.y : (j & 3u) == 2 ? w.z : w.w;
+        const uint32_t c = draw_index(to_uniform(x), nf, n);
+        const float sc = __ldg(score + c);
+        if (i == 0 || sbest < sc) { best = c; sbest = sc; }
+    }
+    return best;
 }
 
 // per-block best: warp shuffles, then one atomic per block
@@ -135,8 +157,13 @@ __global__ void __launch_bounds__(128) generation_hooks(const __grid_constant__ 
             bulk_load(s_child, a.nxt + (size_t)base * S, nact * row_bytes, bar);
         }
         if (active) {
-            p1 = tournament(a.score_in, u0, u1, a.nf, a.n);  // src/pga.cu:306
-            p2 = tournament(a.score_in, u2, u3, a.nf, a.n);  // src/pga.cu:307
+            if (a.tk == 2u) {
+                p1 = tournament(a.score_in, u0, u1, a.nf, a.n);  // src/pga.cu:306
+                p2 = tournament(a.score_in, u2, u3, a.nf, a.n);  // src/pga.cu:307
+            } else {
+                p1 = tournament_of(a.draw, a.score_in, i, 0u, a.tk, a.nf, a.n);
+                p2 = tournament_of(a.draw, a.score_in, i, a.tk, a.tk, a.nf, a.n);
+            }
             if (a.sel) { a.sel[2 * (size_t)i] = (int32_t)p1; a.sel[2 * (size_t)i + 1] = (int32_t)p2; }
             if (stage_parents) {
                 bulk_load(s_p1 + (size_t)t * S, a.cur + (size_t)p1 * S, row_bytes, bar);
@@ -295,8 +322,13 @@ __global__ void __launch_bounds__(256) generation_fast(const __grid_constant__ G
             const uint4 w = draw_block(a.draw, STREAM_ROW, mine, 0);
             const float u0 = to_uniform(w.x), u1 = to_uniform(w.y), u2 = to_uniform(w.z), u3 = to_uniform(w.w);
             if (PH & PH_CROSSOVER) {
-                p1 = tournament(a.score_in, u0, u1, a.nf, a.n);
-                p2 = tournament(a.score_in, u2, u3, a.nf, a.n);
+                if (a.tk == 2u) {
+                    p1 = tournament(a.score_in, u0, u1, a.nf, a.n);
+                    p2 = tournament(a.score_in, u2, u3, a.nf, a.n);
+                } else {
+                    p1 = tournament_of(a.draw, a.score_in, mine, 0u, a.tk, a.nf, a.n);
+                    p2 = tournament_of(a.draw, a.score_in, mine, a.tk, a.tk, a.nf, a.n);
+                }
                 if (a.sel) { a.sel[2 * (size_t)mine] = (int32_t)p1; a.sel[2 * (size_t)mine + 1] = (int32_t)p2; }
             }
             if (PH & PH_MUTATE) {
@@ -806,6 +838,29 @@ __global__ void __launch_bounds__(256) reduce_best(const float* __restrict__ sco
         key = k > key ? k : key;
     }
     block_best_commit(key, best + slot, warp_best);
+}
+
+// ---- best score over several populations' slots (early-stop check) ------------------
+struct BestSlots {
+    const unsigned long long* slot[10];  // MAX_POPULATIONS
+    uint32_t count;
+};
+
+// inverse of order_key: the score a best-key was built from (an empty slot or NaN gives -inf)
+__device__ __forceinline__ float score_of_key(unsigned long long key)
+{
+    const uint32_t k = (uint32_t)(key >> 32);
+    if (k == 0u) return -INFINITY;
+    return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k);
+}
+
+__global__ void best_of_slots(const BestSlots s, float* out)
+{
+    if (threadIdx.x == 0) {
+        float best = -INFINITY;
+        for (uint32_t i = 0; i < s.count; ++i) best = fmaxf(best, score_of_key(*s.slot[i]));
+        *out = best;
+    }
 }
 
 // ---- top-k radix select ------------------------------------------------------------

@@ -218,6 +218,11 @@ struct opga {
 	int topology;
 	unsigned delay;
 	uint32_t migrate_round;
+	unsigned tournament; /* candidates per parent; 2 = TOURNAMENT_POPULATION, src/pga.cu:278 */
+	int target_armed;    /* include/pga.h:141, :147: "... or obj_func(best_genome) == value" */
+	float target_value;
+	unsigned target_every;
+	unsigned generations_run;
 };
 
 opga_t *opga_init(uint64_t seed) /* src/pga.cu:148-164 */
@@ -228,6 +233,7 @@ opga_t *opga_init(uint64_t seed) /* src/pga.cu:148-164 */
 	p->seed = seed;
 	p->threads = 1;
 	p->delay = 1;
+	p->tournament = 2;
 	p->topology = OPGA_TOPO_RANDOM; /* "random migrations", include/pga.h:148 */
 	return p;
 }
@@ -343,6 +349,22 @@ static inline long tournament(const float *score, float ua, float ub, unsigned l
 	return score[a] < score[b] ? b : a;
 }
 
+/* src/pga.cu:280-292 with TOURNAMENT_POPULATION = K: candidates from draws first..first+K-1
+ * of the individual's rand row; a later candidate wins only if strictly better */
+static long tournament_of(const opga_t *p, const opga_pop_t *q, uint32_t individual, unsigned first, unsigned K)
+{
+	long best = -1;
+	for (unsigned i = 0; i < K; ++i) {
+		float u = opga_draw_uniform(p->seed, q->island, q->epoch, individual, first + i);
+		long c = draw_index(u, q->size);
+		if (best == -1 || q->score[best] < q->score[c])
+			best = c;
+	}
+	return best;
+}
+
+void opga_set_tournament(opga_t *p, unsigned k) { p->tournament = k ? k : 2; }
+
 /* src/pga.cu:294-325 with the default operator of :135-143 */
 void opga_crossover(opga_t *p, opga_pop_t *q)
 {
@@ -350,8 +372,14 @@ void opga_crossover(opga_t *p, opga_pop_t *q)
 	for (long i = 0; i < (long)q->size; ++i) {
 		float u[4];
 		opga_rand_row(p->seed, q->island, q->epoch, (uint32_t)i, 4, u);
-		long a = tournament(q->score, u[0], u[1], q->size);
-		long b = tournament(q->score, u[2], u[3], q->size);
+		long a, b;
+		if (p->tournament == 2) {
+			a = tournament(q->score, u[0], u[1], q->size); /* src/pga.cu:306 */
+			b = tournament(q->score, u[2], u[3], q->size); /* src/pga.cu:307 */
+		} else {
+			a = tournament_of(p, q, (uint32_t)i, 0, p->tournament);
+			b = tournament_of(p, q, (uint32_t)i, p->tournament, p->tournament);
+		}
 		q->sel[2 * i] = (int32_t)a;
 		q->sel[2 * i + 1] = (int32_t)b;
 		const uint32_t *p1 = q->cur + (size_t)a * q->row_words;
@@ -442,12 +470,54 @@ static void one_generation(opga_t *p, opga_pop_t *q) /* body of src/pga.cu:381-3
 	opga_swap_generations(p, q);
 }
 
+/* include/pga.h:141, :147: run "until n-generations or obj_func(best_genome) == value".  No
+ * signature carries the value and the reference has no such code; fixed here: after every
+ * generation g that is a multiple of `every` (g < n) the run ends if the best score of any
+ * population is >= value.  every = 0 disarms. */
+void opga_set_target(opga_t *p, float value, unsigned every)
+{
+	p->target_armed = every != 0;
+	p->target_value = value;
+	p->target_every = every;
+}
+
+unsigned opga_generations_run(opga_t *p) { return p->generations_run; }
+
+static int target_reached(opga_t *p, unsigned g, unsigned n)
+{
+	if (!p->target_armed || g % p->target_every != 0 || g >= n)
+		return 0;
+	for (unsigned s = 0; s < p->p_count; ++s) {
+		opga_pop_t *q = p->populations[s];
+		if (q->size == 0)
+			continue;
+		if (!q->scores_valid)
+			opga_evaluate(p, q);
+		float best;
+		opga_best_index(p, q, &best);
+		if (best >= p->target_value)
+			return 1;
+	}
+	return 0;
+}
+
 void opga_run(opga_t *p, unsigned n) /* src/pga.cu:376-391 */
 {
 	if (p->p_count == 0)
 		return;
-	for (unsigned i = 0; i < n; ++i)
+	/* pga_run works on populations[0] only (src/pga.cu:382-386); so does its stop test */
+	unsigned keep = p->p_count, g;
+	p->generations_run = n;
+	for (g = 1; g <= n; ++g) {
 		one_generation(p, p->populations[0]);
+		p->p_count = 1;
+		int stop = target_reached(p, g, n);
+		p->p_count = keep;
+		if (stop) {
+			p->generations_run = g;
+			break;
+		}
+	}
 	opga_evaluate(p, p->populations[0]);
 }
 
@@ -753,7 +823,16 @@ void opga_run_islands(opga_t *p, unsigned n, unsigned m, float pct)
 			if (p->delay == 0)
 				finish_exchange(p, &pm);
 		}
+		if (target_reached(p, g, n)) { /* include/pga.h:147 */
+			p->generations_run = g;
+			if (pm.active) /* an exchange in flight never lands */
+				for (unsigned s = 0; s < p->p_count; ++s) {
+					free(pm.rows[s]); free(pm.scores[s]);
+				}
+			return;
+		}
 	}
+	p->generations_run = n;
 }
 
 /* ---- raw access ----------------------------------------------------------- */

@@ -86,6 +86,9 @@ void opga_mutate(opga_t *, opga_pop_t *);
 void opga_mutate_all(opga_t *);
 void opga_swap_generations(opga_t *, opga_pop_t *);
 void opga_fill_random_values(opga_t *, opga_pop_t *);
+void opga_set_tournament(opga_t *, unsigned k);                      /* candidates per parent (2 = the reference) */
+void opga_set_target(opga_t *, float value, unsigned check_every);   /* include/pga.h:141, :147 */
+unsigned opga_generations_run(opga_t *);
 void opga_run(opga_t *, unsigned n);
 void opga_migrate(opga_t *, float pct);
 void opga_migrate_between(opga_t *, opga_pop_t *, opga_pop_t *, float pct);

@@ -72,6 +72,9 @@ def lib():
         "opga_swap_generations": (None, [vp, vp]),
         "opga_fill_random_values": (None, [vp, vp]),
         "opga_run": (None, [vp, ui]),
+        "opga_set_tournament": (None, [vp, ui]),
+        "opga_set_target": (None, [vp, f32, ui]),
+        "opga_generations_run": (ui, [vp]),
         "opga_migrate": (None, [vp, f32]),
         "opga_migrate_between": (None, [vp, vp, vp, f32]),
         "opga_set_topology": (None, [vp, i32]),
@@ -255,6 +258,12 @@ class Oracle:
     def swap_generations(self, pop): self.L.opga_swap_generations(self.h, pop.h)
     def fill_random_values(self, pop): self.L.opga_fill_random_values(self.h, pop.h)
     def run(self, n): self.L.opga_run(self.h, n)
+    def set_tournament(self, k): self.L.opga_set_tournament(self.h, k)
+    def set_target(self, value, check_every=1): self.L.opga_set_target(self.h, value, check_every)
+
+    @property
+    def generations_run(self): return int(self.L.opga_generations_run(self.h))
+
     def migrate(self, pct): self.L.opga_migrate(self.h, pct)
     def migrate_between(self, a, b, pct): self.L.opga_migrate_between(self.h, a.h, b.h, pct)
     def set_topology(self, t): self.L.opga_set_topology(self.h, t)

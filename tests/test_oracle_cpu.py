@@ -140,6 +140,54 @@ def test_oracle_edge_cases(oracle):
     o.close()
 
 
+def test_tournament_sizes(oracle):
+    # src/pga.cu:280-292 with TOURNAMENT_POPULATION = K: candidates from draws 0..K-1 and K..2K-1
+    seed = 17
+    for k in (1, 2, 3, 5):
+        o = oracle.Oracle(seed)
+        p = o.create_population(400, 16)
+        o.set_objective_hook("sum_obj")
+        o.set_tournament(k)
+        o.fill_random_values(p)
+        o.evaluate(p)
+        o.crossover(p)
+        s, sel = p.scores(), p.selection()
+        for i in (0, 7, 399):
+            u = oracle.rand_row(seed, 0, p.epoch, i, 2 * k)
+            cand = [min(int(np.float32(x) * np.float32(400)), 399) for x in u]
+            for which, group in enumerate((cand[:k], cand[k:])):
+                best = group[0]
+                for c in group[1:]:
+                    if s[best] < s[c]:
+                        best = c
+                assert sel[i, which] == best
+        o.close()
+
+
+def test_target_stop(oracle):
+    # include/pga.h:141: "until n-generations or obj_func(best_genome) == value"
+    a = oracle.Oracle(3)
+    pa = a.create_population(512, 128, oracle.GENES_BITS)
+    a.set_builtin_objective(oracle.OBJ_ONEMAX)
+    a.set_target(84.0, 2)
+    a.run(100)
+    g = a.generations_run
+    assert 0 < g < 100 and g % 2 == 0
+    assert a.best_index(pa)[1] >= 84.0
+    b = oracle.Oracle(3)
+    pb = b.create_population(512, 128, oracle.GENES_BITS)
+    b.set_builtin_objective(oracle.OBJ_ONEMAX)
+    b.run(g)                               # the stopped run is the plain run of g generations
+    assert np.array_equal(pa.genes(), pb.genes())
+    b2 = oracle.Oracle(3)
+    p2 = b2.create_population(512, 128, oracle.GENES_BITS)
+    b2.set_builtin_objective(oracle.OBJ_ONEMAX)
+    b2.run(g - 2)                          # and two generations earlier the target was not met
+    assert b2.best_index(p2)[1] < 84.0
+    for x in (a, b, b2):
+        x.close()
+
+
 def test_select_top_order_and_ties(oracle):
     s = np.array([3, 7, 7, 1, np.nan, 7, 0, -0.0], dtype=np.float32)
     assert list(oracle.select_top(s, 2)) == [1, 2]              # lower index wins ties
