@@ -14,9 +14,16 @@ islands form a ring and the top 1 % migrate every 10 generations over NCCL
 Prints ONE JSON line (rank 0).  value = genome-evaluations/s with the population
 resident in HBM; e2e = the same through the public API with the initial
 population uploaded from pinned host memory and the best individual read back
-every step.  --impl reference times the CPU oracle (the reference has no CPU
-implementation of its own; its GPU code is a 2013 sm_20 build that cannot run
-this workload) on all host cores.
+every step.  Two sub-records ride on the same line:
+  c5               BASELINE config 5 as written: 8 islands x 2^22 x 1024 bits spread 8/N per
+                   GPU, ring, top 1 % (41 943 rows) every 10 generations, 20 generations per
+                   step, CUDA-event timed (skip with --no-c5)
+  islands_parity   at N > 1: a small ring (one 20 000 x 1024-bit island per GPU, 23
+                   generations, top 1 % every 5) run over NCCL and replayed on the CPU
+                   oracle outside the timed region; ok = every island bit-identical
+--impl reference times the CPU oracle (the reference has no CPU implementation of its own
+and its GPU kernels cannot launch this workload: genome_len > 192, src/pga.cu:66-70) on
+all host cores; at --gpus N it runs the same N-island ring (o.run_islands).
 """
 import argparse
 import json
@@ -156,8 +163,11 @@ def run_reference_arm(args, w, emit):
     from oracle import pyoracle as po
     cores = os.cpu_count() or 1
     enc = po.GENES_BITS if w["bits"] else po.GENES_F32
+    # the same island layout as our arm: one island per GPU, ring, top pct every m generations
+    n_islands = max(1, args.gpus) * args.islands
+    ring = n_islands > 1
     o = po.Oracle(42, threads=cores)
-    pop = o.create_population(w["size"], w["length"], enc)
+    pops = [o.create_population(w["size"], w["length"], enc) for _ in range(n_islands)]
     if w.get("builtin"):
         o.set_builtin_objective(getattr(po, "OBJ_" + w["builtin"]))
     if w.get("hook"):
@@ -170,27 +180,42 @@ def run_reference_arm(args, w, emit):
             tok = f.read().split()
         n = int(tok[0])
         o.tsp_load(np.array(tok[1:1 + n * n], dtype=np.float32).reshape(n, n))
-    o.evaluate(pop)
+    o.set_topology(po.TOPO_RING)
+    o.evaluate_all()
+
+    def step(gens):
+        if ring:
+            o.run_islands(gens, args.migrate_every, args.migrate_pct)
+        else:
+            o.run(gens)
+
     # size the per-step sample so the whole run stays within a few minutes
-    t0 = time.perf_counter(); o.run(1); per_gen = time.perf_counter() - t0
+    t0 = time.perf_counter(); step(1); per_gen = time.perf_counter() - t0
     budget = 120.0 / max(1, args.steps + args.warmup)
     gens = max(1, min(args.gens, int(budget / max(per_gen, 1e-6))))
+    if ring and gens > args.migrate_every:  # whole migration periods, so every step holds the same number of exchanges
+        gens -= gens % args.migrate_every
     for _ in range(args.warmup):
-        o.run(gens)
+        step(gens)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        o.run(gens)
+        step(gens)
     dt = time.perf_counter() - t0
-    value = args.steps * gens * w["size"] / dt
-    sample = f"{gens} generations of {w['label']} per step at full population size, OpenMP over individuals"
+    value = args.steps * gens * w["size"] * n_islands / dt
+    sample = (f"{gens} generations of {w['label']} per step at full population size, {n_islands} island(s)"
+              + (f", ring, top {args.migrate_pct}% every {args.migrate_every} generations" if ring else "") + ", OpenMP over individuals")
     o.close()
     line = {
         "impl": "reference", "metric": "genome-evaluations/sec", "value": value, "unit": "evals/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u32" if w["bits"] else "f32", "data": "synthetic",
         "generations_per_sec": args.steps * gens / dt,
-        "config": {"workload": w["label"], "generations_per_step": gens, "seed": 42,
-                   "note": "CPU oracle (oracle/pga_oracle.c): the reference has no CPU path and its sm_20 GPU build cannot run this workload"},
+        "config": {"workload": w["label"], "generations_per_step": gens, "islands": n_islands, "islands_per_gpu": args.islands, "seed": 42,
+                   "operators": "tournament-2, uniform crossover, p=0.01 single-gene mutation",
+                   "migration": f"ring, top {args.migrate_pct}% every {args.migrate_every} generations (CPU)" if ring else "none (single island)",
+                   "l2": "n/a (host memory)",
+                   "note": "CPU oracle (oracle/pga_oracle.c): the reference has no CPU path and its own GPU kernels cannot launch this "
+                           "workload (genome_len > 192, src/pga.cu:66-70); generations_per_step is a bounded sample of our arm's"},
         "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -224,6 +249,81 @@ def cpu_baseline(w, cores=None):
             "sample": f"{gens} generations at full population size ({w['label']}), oracle/pga_oracle.c with OpenMP over individuals, {dt:.1f} s"}
 
 
+def run_c5(args, pg, islands, dist, torch, stream, world, distributed):
+    """BASELINE config 5 as written: 8 islands x 2^22 x 1024 bits over the GPUs, ring, top 1 %
+    (41 943 rows) every 10 generations; 20 generations per step; CUDA events, max over ranks."""
+    per_gpu = max(1, 8 // world)
+    size, bits, gens, every, pct = 1 << 22, 1024, 20, 10, 1.0
+    g = pg.PGA(seed=42)
+    g.set_stream(stream.cuda_stream)
+    if distributed:
+        islands.rendezvous(g, dist)
+    g.set_topology(pg.TOPO_RING)
+    pops = [g.create_population(size, bits, encoding=pg.GENES_BITS) for _ in range(per_gpu)]
+    g.set_builtin_objective(pg.OBJ_ONEMAX)
+    g.evaluate_all()
+    for _ in range(3):
+        g.run_islands(gens, every, pct)
+    if distributed:
+        dist.barrier()
+    torch.cuda.synchronize()
+    steps = 3
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = g.kernel_launches
+    e0.record(stream)
+    for _ in range(steps):
+        g.run_islands(gens, every, pct)
+    e1.record(stream)
+    if distributed:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if distributed:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+    launches = g.kernel_launches - launches0
+    assert pg.migration_count(size, pct) == 41943
+    g.deinit()
+    total_islands = per_gpu * world
+    return {"workload": "BASELINE config 5: %d islands x 2^22 x 1024 bits, ring, top 1%% (41943 rows) every 10 generations" % total_islands,
+            "value": steps * gens * size * total_islands / (ms * 1e-3), "unit": "evals/s", "ms_per_step": ms / steps,
+            "generations_per_step": gens, "steps": steps, "islands": total_islands, "islands_per_gpu": per_gpu, "n_gpus": world,
+            "exchanges_per_step": 1, "gpu_launches": launches}
+
+
+def run_islands_parity(pg, islands, dist, rank, world):
+    """One 20 000 x 1024-bit island per GPU, ring over NCCL, 23 generations, top 1 % every 5;
+    rank 0 replays all islands on the CPU oracle and compares digests island by island."""
+    from oracle import pyoracle as po
+    seed, size, bits, gens, every, pct = 123, 20000, 1024, 23, 5, 1.0
+    g = pg.PGA(seed=seed)
+    islands.rendezvous(g, dist)
+    g.set_topology(pg.TOPO_RING)
+    pop = g.create_population(size, bits, encoding=pg.GENES_BITS)
+    g.set_builtin_objective(pg.OBJ_ONEMAX)
+    g.run_islands(gens, every, pct)
+    mine = {pop.island: (po.digest(pop.genes()), po.digest(pop.scores()))}
+    gathered = [None] * world
+    dist.all_gather_object(gathered, mine)
+    g.deinit()
+    if rank != 0:
+        return None
+    got = {}
+    for d in gathered:
+        got.update(d)
+    o = po.Oracle(seed, threads=os.cpu_count() or 1)
+    o.set_builtin_objective(po.OBJ_ONEMAX)
+    ops = [o.create_population(size, bits, po.GENES_BITS) for _ in range(world)]
+    o.set_topology(po.TOPO_RING)
+    o.run_islands(gens, every, pct)
+    bad = [i for i, p in enumerate(ops) if got.get(i) != (po.digest(p.genes()), po.digest(p.scores()))]
+    o.close()
+    return {"checked": True, "ok": not bad, "islands": world, "mismatched_islands": bad,
+            "what": "one 20000 x 1024-bit island per GPU, NCCL ring, 23 generations, top 1% every 5; every island's genomes and scores "
+                    "compared bit for bit with oracle/pga_oracle.c (outside the timed region)"}
+
+
 def main():
     # the contract is ONE JSON line on stdout: libraries (NCCL prints its version banner
     # to stdout) must not get there, so fd 1 points at stderr until the line is ready
@@ -245,6 +345,7 @@ def main():
     ap.add_argument("--islands", type=int, default=1, help="islands per GPU (BASELINE config 5: 8 islands over N GPUs)")
     ap.add_argument("--migrate-every", type=int, default=10)
     ap.add_argument("--migrate-pct", type=float, default=1.0)
+    ap.add_argument("--no-c5", action="store_true", help="skip the BASELINE config 5 sub-record")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     w = dict(WORKLOADS[args.workload])
@@ -358,7 +459,8 @@ def main():
         "config": {"workload": w["label"], "generations_per_step": args.gens, "islands": world * args.islands, "islands_per_gpu": args.islands, "seed": 42,
                    "operators": "tournament-2, uniform crossover, p=0.01 single-gene mutation",
                    "migration": f"ring, top {args.migrate_pct}% every {args.migrate_every} generations over NCCL" if (distributed or args.islands > 1) else "none (single island)",
-                   "l2": "inputs larger than L2: two generations of the population = %.0f MiB vs 126 MB" % (2 * w["size"] * gb / 2 ** 20)},
+                   "l2": "inputs larger than L2: two generations of the population = %.0f MiB vs 126 MB" % (2 * w["size"] * gb / 2 ** 20),
+                   "note": "CUDA library through the C-ABI; no CPU path"},
         "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "what": "upload population (pinned host) + pga_run/pga_run_islands + pga_get_best, wall clock"},
         "gpu_launches": launches,
@@ -369,10 +471,18 @@ def main():
                      "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
                      "note": FABRIC_NOTE.get(args.workload)},
     }
+    g.deinit()
+    if args.workload == "onemax" and not args.no_c5 and not args.size:
+        c5 = run_c5(args, pg, islands, dist, torch, stream, world, distributed)
+        line["c5"] = c5
+    if distributed:
+        parity = run_islands_parity(pg, islands, dist, rank, world)
+        line["islands_parity"] = parity
+    else:
+        line["islands_parity"] = {"checked": False, "why": "single GPU: no NCCL exchange to check (tests/test_gpu_islands.py covers the one-GPU islands)"}
     if rank == 0 and not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline(w)                  # all host cores (OpenMP over individuals)
         line["cpu_baseline_serial"] = cpu_baseline(w, cores=1)  # the serial oracle, one core
-    g.deinit()
     if distributed:
         dist.barrier()
         dist.destroy_process_group()

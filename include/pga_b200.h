@@ -160,7 +160,7 @@ int pgax_select_top(pga_t *, population_t *, unsigned long k, int worst, uint32_
  * pool, or a loop that cannot take the device-wide stall of cudaMalloc/cudaFree.
  * It needs no solver and no population: `dev_scores` (n floats) and `dev_indices`
  * (room for min(k, n) indices) are DEVICE pointers supplied by the caller, and the
- * working memory is a fixed 66 KB array inside the library image, held by every
+ * working memory is a fixed 72 KB array inside the library image, held by every
  * GPU that loads the library until the process exits.  Same result and order as
  * pgax_select_top.  Rules:
  *   - n may not exceed PGAX_NOALLOC_MAX_INDIVIDUALS; larger inputs return

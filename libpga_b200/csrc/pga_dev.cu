@@ -22,6 +22,7 @@
 #include "../../include/pga_b200.h"
 #include "pga_dev.h"
 #include "pga_kernels.cuh"
+#include "pga_kernel_sorted.cuh"
 
 using namespace pgak;
 
@@ -49,16 +50,15 @@ struct pgadev_ctx {
     uint32_t fast_blocks_per_sm;  // $PGA_FAST_BLOCKS_PER_SM: grid cap of the fast kernels
     int fast_blocks_per_sm_set;
     int force_generic;            // $PGA_FORCE_GENERIC=1: skip the compile-time tiled kernels
-    int staged;                   // $PGA_STAGED=1: small rows take the cp.async-staged kernel instead
     int no_hook_split;            // $PGA_NO_HOOK_SPLIT=1: generations with hooks are always one launch
     int no_coop;                  // $PGA_NO_COOP=1: rank with the 5-launch select instead of the cooperative kernel
     uint32_t reserve_now;         // SMs' worth of blocks the current launch leaves free (pgadev_step.reserve_sms)
+    int sorted;                   // $PGA_SORTED: long rows visited in first-parent order (0 = off, 1 = on, 2 = alternative occupancy)
+    uint32_t side_blocks;         // $PGA_SIDE_BLOCKS: grid of a ranking that runs beside a generation (default 64)
     // early-stop check (pgax_set_target): best score of the local populations
     float* check_dev;
     float* check_host;  // pinned
     cudaEvent_t ev_check;
-    int l2_persist;               // $PGA_L2_PERSIST: 1 = children being written persist in L2, 2 = the parents' buffer does (experiment)
-    size_t l2_window_max;
 };
 
 struct pgadev_pop {
@@ -90,6 +90,10 @@ struct pgadev_pop {
     // migration boxes
     uint32_t *outbox, *inbox;
     uint64_t box_cap;
+    // first-parent-ordered generation (pga_kernel_sorted.cuh): pairs, counts/offsets, block offsets, records
+    uint2* srt_pair;
+    uint32_t *srt_count, *srt_block;
+    uint4* srt_rec;
     // host <-> device staging for padded rows
     uint32_t* stage;
     size_t stage_bytes;
@@ -145,14 +149,10 @@ extern "C" pgadev_ctx* pgadev_ctx_create(void)
     c->fast_blocks_per_sm = (e = getenv("PGA_FAST_BLOCKS_PER_SM")) && atoi(e) > 0 ? (uint32_t)atoi(e) : 16u;
     c->fast_blocks_per_sm_set = e && atoi(e) > 0;
     c->force_generic = (e = getenv("PGA_FORCE_GENERIC")) ? atoi(e) : 0;
-    c->staged = (e = getenv("PGA_STAGED")) ? atoi(e) : 0;
     c->no_hook_split = (e = getenv("PGA_NO_HOOK_SPLIT")) ? atoi(e) : 0;
     c->no_coop = (e = getenv("PGA_NO_COOP")) ? atoi(e) : 0;
-    c->l2_persist = (e = getenv("PGA_L2_PERSIST")) ? atoi(e) : 0;
-    if (c->l2_persist) {
-        CCE(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize));
-        c->l2_window_max = (size_t)prop.accessPolicyMaxWindowSize;
-    }
+    c->sorted = (e = getenv("PGA_SORTED")) ? atoi(e) : 0;
+    c->side_blocks = (e = getenv("PGA_SIDE_BLOCKS")) && atoi(e) > 0 ? (uint32_t)atoi(e) : 64u;
     const char* stack = getenv("PGA_STACK_BYTES");  // device stack for deep user hooks
     if (stack && atoi(stack) > 0) CCE(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(stack)));
     return c;
@@ -254,6 +254,10 @@ extern "C" void pgadev_pop_destroy(pgadev_ctx* c, pgadev_pop* p)
     if (p->outbox) CCE(cudaFree(p->outbox));
     if (p->inbox) CCE(cudaFree(p->inbox));
     if (p->stage) CCE(cudaFree(p->stage));
+    if (p->srt_pair) CCE(cudaFree(p->srt_pair));
+    if (p->srt_count) CCE(cudaFree(p->srt_count));
+    if (p->srt_block) CCE(cudaFree(p->srt_block));
+    if (p->srt_rec) CCE(cudaFree(p->srt_rec));
     free(p);
 }
 
@@ -398,21 +402,13 @@ template <int ENC, int OBJ, int LOGG, int NB, bool EXACT>
 static int launch_tiled_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
     constexpr int TB = TiledShape<ENC, LOGG, NB>::TB, MINB = TiledShape<ENC, LOGG, NB>::MINB;
-    // occupancy per device ordinal: a second thread or solver on another device reads its
-    // own entry (a racing first use writes the same value twice)
-    static int occupancy[MAX_DEVICES];
-    int blocks_per_sm = occupancy[c->device % MAX_DEVICES];
-    if (blocks_per_sm == 0) {
-        CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, generation_fused_tiled<ENC, OBJ, LOGG, NB, TB, EXACT, MINB>, 256, 0));
-        if (blocks_per_sm < 1) blocks_per_sm = 1;
-        occupancy[c->device % MAX_DEVICES] = blocks_per_sm;
-    }
-    // exactly one resident wave (a partial second wave costs a full kernel tail), minus
-    // the blocks held back so that side-stream work can run beside this launch
-    const uint32_t per_sm = c->fast_blocks_per_sm_set ? c->fast_blocks_per_sm : (uint32_t)blocks_per_sm;
+    constexpr uint32_t THREADS = 256u * MINB;
+    // exactly one resident wave, one block per SM (a partial second wave costs a full kernel
+    // tail), minus the SMs held back so that side-stream work can run beside this launch
+    const uint32_t per_sm = c->fast_blocks_per_sm_set ? c->fast_blocks_per_sm : 1u;
     const uint32_t sms = (uint32_t)c->sm_count - (c->reserve_now < (uint32_t)c->sm_count / 2u ? c->reserve_now : (uint32_t)c->sm_count / 2u);
-    const uint32_t grid = grid_for(p->n, 256, sms * per_sm);
-    generation_fused_tiled<ENC, OBJ, LOGG, NB, TB, EXACT, MINB><<<grid, 256, 0, c->stream>>>(a);
+    const uint32_t grid = grid_for(p->n, THREADS, sms * per_sm);
+    generation_fused_tiled<ENC, OBJ, LOGG, NB, TB, EXACT, MINB><<<grid, THREADS, 0, c->stream>>>(a);
     LAUNCH_CHECK(c);
     return 0;
 }
@@ -425,42 +421,54 @@ static int launch_tiled_inst(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
     return exact ? launch_tiled_one<ENC, OBJ, LOGG, NB, true>(c, p, a) : launch_tiled_one<ENC, OBJ, LOGG, NB, false>(c, p, a);
 }
 
-// small rows (32..128 B): per-warp cp.async pipeline through shared memory,
-// selectable with $PGA_STAGED=1 (measured alternative)
-template <int ENC, int OBJ, int LOGG, bool EXACT, int MINB>
-static int launch_staged_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+// ---- long rows: children visited in first-parent order (pga_kernel_sorted.cuh) ---------------------
+template <int ENC, int OBJ, int NB, bool EXACT, int MINB>
+static int launch_sorted_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
-    constexpr int WARPS = 4;
-    constexpr size_t smem = (size_t)WARPS * 2u * 32u * (16u << LOGG);
-    static int occupancy[MAX_DEVICES];
-    int blocks_per_sm = occupancy[c->device % MAX_DEVICES];
-    if (blocks_per_sm == 0) {
-        CCE(cudaFuncSetAttribute(generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS, MINB>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS, MINB>,
-                                                          WARPS * 32, smem));
-        if (blocks_per_sm < 1) blocks_per_sm = 1;
-        occupancy[c->device % MAX_DEVICES] = blocks_per_sm;
+    const uint32_t n = (uint32_t)p->n;
+    const uint32_t nbk = (n + SORTED_SCAN_CHUNK - 1u) / SORTED_SCAN_CHUNK;
+    if (!p->srt_rec) {
+        CCE(cudaMalloc((void**)&p->srt_pair, (size_t)n * sizeof(uint2)));
+        CCE(cudaMalloc((void**)&p->srt_count, (size_t)n * sizeof(uint32_t)));
+        CCE(cudaMalloc((void**)&p->srt_block, (size_t)(nbk + 1u) * sizeof(uint32_t)));
+        CCE(cudaMalloc((void**)&p->srt_rec, (size_t)n * sizeof(uint4)));
     }
-    const uint32_t grid = grid_for(p->n, WARPS * 32u, (uint32_t)(c->sm_count * blocks_per_sm));
-    generation_fused_staged<ENC, OBJ, LOGG, EXACT, WARPS, MINB><<<grid, WARPS * 32, smem, c->stream>>>(a);
+    const uint32_t sms = (uint32_t)c->sm_count - (c->reserve_now < (uint32_t)c->sm_count / 2u ? c->reserve_now : (uint32_t)c->sm_count / 2u);
+    const uint32_t wide = grid_for(n, 256, sms * 8u);
+    CCE(cudaMemsetAsync(p->srt_count, 0, (size_t)n * sizeof(uint32_t), c->stream));
+    sorted_select<<<wide, 256, 0, c->stream>>>(a, p->srt_pair, p->srt_count);
+    LAUNCH_CHECK(c);
+    sorted_scan_local<<<nbk, SORTED_SCAN_BLOCK, 0, c->stream>>>(p->srt_count, n, p->srt_block);
+    LAUNCH_CHECK(c);
+    sorted_scan_totals<<<1, 1024, 0, c->stream>>>(p->srt_block, nbk);
+    LAUNCH_CHECK(c);
+    sorted_scatter<<<wide, 256, 0, c->stream>>>(p->srt_pair, n, p->srt_count, p->srt_block, p->srt_rec);
+    LAUNCH_CHECK(c);
+    GenArgs g = a;
+    g.sel = nullptr;  // sorted_select has written the capture
+    const uint32_t grid = grid_for((n + 31u) / 32u, 8u * MINB, sms);
+    generation_sorted<ENC, OBJ, NB, EXACT, MINB><<<grid, 256 * MINB, 0, c->stream>>>(g, p->srt_rec);
     LAUNCH_CHECK(c);
     return 0;
 }
 
+// rows of more than 256 bytes (32 lanes per child), up to four 16-byte blocks per lane; 1 = not applicable
 template <int ENC, int OBJ>
-static int launch_staged(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
+static int launch_sorted(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
-    const uint32_t nblk = p->stride >> 2, G = p->group;
-    if (!c->staged || c->force_generic || nblk > G || G > 8 || G < 2) return 1;
-    const bool exact = nblk == G && (ENC == ENC_BITS || p->len == p->stride);
-#define ST(L) return exact ? launch_staged_one<ENC, OBJ, L, true, 4>(c, p, a) : launch_staged_one<ENC, OBJ, L, false, 4>(c, p, a)
-    switch (G) {
-        case 2: ST(1);
-        case 4: ST(2);
-        default: ST(3);
+    const uint32_t nblk = p->stride >> 2;
+    if (!c->sorted || c->force_generic || p->group != 32u || nblk > 128u || p->n < 8192u) return 1;
+    const uint32_t NBr = (nblk + 31u) / 32u;
+    const bool exact = nblk == NBr * 32u && (ENC == ENC_BITS || p->len == p->stride);
+    const bool alt = c->sorted == 2;
+#define SRT(N, M) return exact ? launch_sorted_one<ENC, OBJ, N, true, M>(c, p, a) : launch_sorted_one<ENC, OBJ, N, false, M>(c, p, a)
+    switch (NBr) {
+        case 1: if (alt) SRT(1, 2); SRT(1, 3);
+        case 2: if (alt) SRT(2, 3); SRT(2, 2);
+        case 3: SRT(3, 2);
+        default: SRT(4, 1);
     }
-#undef ST
+#undef SRT
 }
 
 // Shapes with a compile-time tiling: G = min(32, pow2ceil(blocks)) lanes per child (the
@@ -504,7 +512,7 @@ template <int ENC, int OBJ>
 static int launch_fast_ph(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a, uint32_t ph)
 {
     if (ph == PH_FUSED && a.tk == 2u) {  // the compile-time tilings are built for the reference's size-2 tournament
-        int rc = launch_staged<ENC, OBJ>(c, p, a);
+        int rc = launch_sorted<ENC, OBJ>(c, p, a);
         if (rc <= 0) return rc;
         rc = launch_tiled<ENC, OBJ>(c, p, a);
         if (rc <= 0) return rc;
@@ -548,19 +556,6 @@ extern "C" int pgadev_launch(pgadev_ctx* c, pgadev_pop* p, const pgadev_step* st
     a.mut = (mutate_fn)st->mutate_hook;
     a.xov = (crossover_fn)st->crossover_hook;
 
-    if (c->l2_persist && ph == PH_FUSED) {
-        // experiment: ask L2 to keep one generation buffer resident (access-policy window on the stream)
-        cudaStreamAttrValue v;
-        memset(&v, 0, sizeof(v));
-        size_t bytes = (size_t)p->n * p->stride * 4u;
-        if (bytes > c->l2_window_max) bytes = c->l2_window_max;
-        v.accessPolicyWindow.base_ptr = (void*)((c->l2_persist & 3) == 1 ? (const void*)a.nxt : (const void*)a.cur);
-        v.accessPolicyWindow.num_bytes = bytes;
-        v.accessPolicyWindow.hitRatio = (c->l2_persist & 4) ? 0.6f : 1.0f;
-        v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-        v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-        CCE(cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &v));
-    }
     const bool uses_xov = (ph & PH_CROSSOVER) && a.xov, uses_mut = (ph & PH_MUTATE) && a.mut;
     const bool scores = (ph & PH_EVALUATE) != 0;
     int rc;
@@ -758,6 +753,23 @@ static bool select_top_coop(pgadev_ctx* c, pgadev_pop* p, uint32_t k, int worst,
 
 extern "C" void pgadev_route_to_side(pgadev_ctx* c, int on) { c->route_side = on; }
 
+// five launches: three radix passes (the last block of each picks the digit), the per-chunk
+// counts (the last block scans them), the stable compaction.  grid_cap = 0: one block per chunk.
+static void launch_select_5(pgadev_ctx* c, const float* score, uint32_t n, uint32_t k, int worst, TopkState2* st, uint32_t* bg,
+                            uint32_t* be, uint32_t* out, uint32_t nb, uint32_t grid_cap, cudaStream_t s)
+{
+    const uint32_t grid = grid_cap && grid_cap < nb ? grid_cap : nb;
+    topk2_histogram<21, 11><<<grid, 256, 0, s>>>(score, n, worst, k, st, nb);
+    topk2_histogram<10, 11><<<grid, 256, 0, s>>>(score, n, worst, k, st, nb);
+    topk2_histogram<0, 10><<<grid, 256, 0, s>>>(score, n, worst, k, st, nb);
+    topk2_count_scan<<<grid, TOPK_BLOCK, 0, s>>>(score, n, worst, st, bg, be, nb);
+    topk2_emit<<<grid, TOPK_BLOCK, 0, s>>>(score, n, worst, st, bg, be, out, nb);
+    if (c) {
+        CCE(cudaPeekAtLastError());
+        c->launches += 5;
+    }
+}
+
 extern "C" void pgadev_select_top(pgadev_ctx* c, pgadev_pop* p, uint64_t k, int worst, int slot)
 {
     use_device(c);
@@ -776,20 +788,14 @@ extern "C" void pgadev_select_top(pgadev_ctx* c, pgadev_pop* p, uint64_t k, int 
     uint32_t *bg = p->blk_gt[slot], *be = p->blk_eq[slot];
     const float* score = p->score[p->sidx];
     const uint32_t n = (uint32_t)p->n;
-    if (select_top_coop(c, p, (uint32_t)k, worst, slot, s)) return;
-    // five launches: three radix passes (the last block of each picks the digit), the
-    // per-block counts (the last block scans them), the stable compaction
-    const uint32_t hgrid = p->nb;  // one 2048-score chunk per block
-    topk2_histogram<21, 11><<<hgrid, 256, 0, s>>>(score, n, worst, (uint32_t)k, st);
-    LAUNCH_CHECK(c);
-    topk2_histogram<10, 11><<<hgrid, 256, 0, s>>>(score, n, worst, (uint32_t)k, st);
-    LAUNCH_CHECK(c);
-    topk2_histogram<0, 10><<<hgrid, 256, 0, s>>>(score, n, worst, (uint32_t)k, st);
-    LAUNCH_CHECK(c);
-    topk2_count_scan<<<p->nb, TOPK_BLOCK, 0, s>>>(score, n, worst, st, bg, be, p->nb);
-    LAUNCH_CHECK(c);
-    topk2_emit<<<p->nb, TOPK_BLOCK, 0, s>>>(score, n, worst, st, bg, be, p->idx[slot]);
-    LAUNCH_CHECK(c);
+    // A ranking routed to the side stream runs BESIDE the next generation, on the few SMs that
+    // kernel left free (pgadev_step.reserve_sms).  The cooperative kernel needs all of its
+    // blocks resident at once and would wait for the generation to drain; the five-launch
+    // form has no inter-block waits, so a small grid-stride grid makes progress in whatever
+    // room there is and has a whole generation of slack.
+    const bool beside_generation = c->route_side != 0;
+    if (!beside_generation && select_top_coop(c, p, (uint32_t)k, worst, slot, s)) return;
+    launch_select_5(c, score, n, (uint32_t)k, worst, st, bg, be, p->idx[slot], p->nb, beside_generation ? c->side_blocks : 0u, s);
 }
 
 extern "C" void pgadev_download_top(pgadev_ctx* c, pgadev_pop* p, int slot, uint64_t k, uint32_t* host_idx)
@@ -1022,7 +1028,7 @@ extern "C" float pgadev_check_wait(pgadev_ctx* c)
 // first use.  Here the caller brings the input and the output, and the only other
 // memory the selection needs -- the radix histogram, the running prefix and the
 // per-block counts -- lives in the fixed array below, which is part of the library
-// image: every GPU that loads the library carries these 66 KB until the process ends.
+// image: every GPU that loads the library carries these 72 KB until the process ends.
 //
 // The array bounds the problem: at most PGAX_NOALLOC_MAX_INDIVIDUALS scores
 // (2^24, i.e. 8192 blocks of 2048).  Larger inputs are refused, not truncated.
@@ -1031,10 +1037,10 @@ extern "C" float pgadev_check_wait(pgadev_ctx* c)
 // handle for the runtime, not an address a kernel could dereference, so the device
 // address is looked up once per device with cudaGetSymbolAddress (with that device
 // current) and that pointer is what the kernels receive.
-#define NOALLOC_STATE_BYTES 2048u  /* TopkState, padded */
+#define NOALLOC_STATE_BYTES 8448u  /* TopkState2 (2048-bin histogram + running state), padded to 256 */
 #define NOALLOC_MAX_BLOCKS ((PGAX_NOALLOC_MAX_INDIVIDUALS + TOPK_CHUNK - 1u) / TOPK_CHUNK)
 #define NOALLOC_SCRATCH_BYTES (NOALLOC_STATE_BYTES + 2u * NOALLOC_MAX_BLOCKS * 4u)
-static_assert(sizeof(TopkState) <= NOALLOC_STATE_BYTES, "scratch layout");
+static_assert(sizeof(TopkState2) <= NOALLOC_STATE_BYTES, "scratch layout");
 
 static __device__ __align__(256) unsigned char noalloc_scratch[NOALLOC_SCRATCH_BYTES];
 
@@ -1071,24 +1077,18 @@ extern "C" int pgax_select_top_noalloc(const float* dev_scores, unsigned long n,
         g_noalloc_ptr[dev] = (unsigned char*)ptr;
     }
     unsigned char* base = g_noalloc_ptr[dev];
-    TopkState* st = reinterpret_cast<TopkState*>(base);
+    TopkState2* st = reinterpret_cast<TopkState2*>(base);
     uint32_t* blk_gt = reinterpret_cast<uint32_t*>(base + NOALLOC_STATE_BYTES);
     uint32_t* blk_eq = blk_gt + NOALLOC_MAX_BLOCKS;
     cudaStream_t s = (cudaStream_t)cuda_stream;
     const uint32_t n32 = (uint32_t)n, nb = (uint32_t)((n + TOPK_CHUNK - 1) / TOPK_CHUNK);
-    const int w = worst ? 1 : 0;
 
-    // the array still holds the previous call's histogram, prefix and block counts:
-    // topk_begin clears the histogram and the running state, topk_pick re-clears the
-    // histogram between passes, and topk_count overwrites all nb block counts
-    topk_begin<<<1, 256, 0, s>>>(st, (uint32_t)k);
-    const uint32_t hgrid = grid_for(n, 256, (uint32_t)g_noalloc_sms[dev] * 8u);
-    for (int pass = 3; pass >= 0; --pass) {
-        topk_histogram<<<hgrid, 256, 0, s>>>(dev_scores, n32, w, (uint32_t)pass * 8u, st);
-        topk_pick<<<1, 256, 0, s>>>(st, (uint32_t)pass * 8u);
-    }
-    topk_count<<<nb, TOPK_BLOCK, 0, s>>>(dev_scores, n32, w, st, blk_gt, blk_eq);
-    topk_scan<<<1, 1024, 0, s>>>(blk_gt, blk_eq, nb);
-    topk_emit<<<nb, TOPK_BLOCK, 0, s>>>(dev_scores, n32, w, st, blk_gt, blk_eq, dev_indices);
+    // The array still holds whatever the previous call left (histogram, prefix, ticket, the
+    // per-chunk counts).  The selection kernels leave the histogram and the ticket clean when
+    // they run to completion, but a call that was cut short would not have: the state is
+    // cleared explicitly, and the count pass overwrites all nb chunk counts before they are read.
+    topk2_reset<<<1, 256, 0, s>>>(st);
+    launch_select_5(NULL, dev_scores, n32, (uint32_t)k, worst ? 1 : 0, st, blk_gt, blk_eq, dev_indices, nb,
+                    (uint32_t)g_noalloc_sms[dev] * 8u, s);
     return cudaPeekAtLastError() == cudaSuccess ? PGAX_OK : PGAX_ECUDA;
 }

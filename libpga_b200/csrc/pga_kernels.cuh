@@ -440,11 +440,16 @@ __global__ void __launch_bounds__(256) generation_fast(const __grid_constant__ G
 // the end of the population are computed from row 0 and only their stores are
 // suppressed, so the loop body has no divergent region around the shuffles.
 // This is the kernel the roofline numbers are quoted on.
+//
+// One block per SM: WPB = 8 * MINB warps in ONE block rather than MINB blocks of 8 warps, so
+// that a grid of (SMs - r) blocks leaves r SMs completely empty -- room for the emigrant
+// ranking, the packing and the NCCL send/recv kernels that run beside a generation on the
+// side stream (two half-filled SMs do not hold an NCCL block; one empty SM does).
 template <int ENC, int OBJ, int LOGG, int NB, int TB, bool EXACT, int MINB>
-__global__ void __launch_bounds__(256, MINB) generation_fused_tiled(const __grid_constant__ GenArgs a)
+__global__ void __launch_bounds__(256 * MINB, 1) generation_fused_tiled(const __grid_constant__ GenArgs a)
 {
     constexpr uint32_t G = 1u << LOGG, CPT = 32u / G;
-    __shared__ unsigned long long warp_best[8];
+    __shared__ unsigned long long warp_best[8 * MINB];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -578,225 +583,6 @@ __global__ void __launch_bounds__(256, MINB) generation_fused_tiled(const __grid
     block_best_commit(key, a.best + a.best_slot, warp_best);
 }
 
-// ---- fused generation, staged (small rows) -------------------------------------
-//
-// For rows of at most 128 bytes (OneMax-1024, short float genomes) the register
-// version above is limited by how many parent loads a warp can keep in flight.
-// Here every warp runs its own three-deep software pipeline over its iterations
-// (32 children each):
-//     iteration i+2 : Philox block 0 + the four score gathers are issued
-//     iteration i+1 : tournaments resolved, both parent rows copied global -> shared
-//                     with 16-byte cp.async (LDGSTS), half an iteration at a time,
-//                     no registers held
-//     iteration i   : rows read back from shared memory, crossover mask drawn,
-//                     child mutated, scored, stored
-// Measured on B200 (scripts/microbench_stage.cu): for 128-byte rows one TMA bulk
-// copy per row is request-rate bound (68 us per 2^20-row pass) while cp.async
-// reaches the same 55 us as plain 128-bit loads, so the small-row path uses
-// cp.async and TMA bulk copies stay on the hook path, where rows are larger.
-struct SelDraw {
-    uint32_t c0, c1, c2, c3;  // tournament candidates
-    float s0, s1, s2, s3;     // their scores (loads in flight until sel_finish)
-    uint32_t m_idx, m_val;    // mutation target and value
-    bool m_on;
-};
-
-template <int ENC>
-__device__ __forceinline__ SelDraw sel_begin(const GenArgs& a, uint32_t child)
-{
-    SelDraw d;
-    const bool have = child < a.n;
-    const uint4 w = draw_block(a.draw, STREAM_ROW, child, 0);
-    const float u0 = to_uniform(w.x), u1 = to_uniform(w.y), u2 = to_uniform(w.z), u3 = to_uniform(w.w);
-    d.c0 = have ? draw_index(u0, a.nf, a.n) : 0u;
-    d.c1 = have ? draw_index(u1, a.nf, a.n) : 0u;
-    d.c2 = have ? draw_index(u2, a.nf, a.n) : 0u;
-    d.c3 = have ? draw_index(u3, a.nf, a.n) : 0u;
-    d.s0 = __ldg(a.score_in + d.c0);
-    d.s1 = __ldg(a.score_in + d.c1);
-    d.s2 = __ldg(a.score_in + d.c2);
-    d.s3 = __ldg(a.score_in + d.c3);
-    d.m_on = have && u1 <= PGA_MUTATION_CHANCE;
-    d.m_idx = draw_index(u0, a.lenf, a.len);
-    d.m_val = ENC == ENC_BITS ? (u2 > 0.5f ? 1u : 0u) : __float_as_uint(u2);
-    return d;
-}
-
-__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
-}
-
-// A warp's iteration is split in two halves of 16 children; each half owns one 4 KB
-// (for 128-byte rows) stage of shared memory, so 8 KB per warp keep ~24 warps per SM
-// resident with one half always in flight while the other is consumed.
-template <int ENC, int OBJ, int LOGG, bool EXACT, int WARPS, int MINB>
-__global__ void __launch_bounds__(WARPS * 32, MINB) generation_fused_staged(const __grid_constant__ GenArgs a)
-{
-    constexpr uint32_t G = 1u << LOGG, CPT = 32u / G, ROW = G * 16u, STAGE = 32u * ROW;  // 16 children x 2 parents
-    constexpr uint32_t HT = G / 2u;  // tiles per half
-    static_assert(LOGG >= 1 && LOGG <= 3, "staged kernel: rows of 32..128 bytes");
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ unsigned long long warp_best[WARPS];
-    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
-    const uint32_t gl = lane & (G - 1u), grp = lane >> LOGG;
-    const uint32_t nblk = EXACT ? G : a.stride >> 2;
-    const bool in_row = EXACT || gl < nblk;
-    unsigned char* const my = smem_raw + (size_t)w * 2u * STAGE;
-    const uint4* __restrict__ cur = reinterpret_cast<const uint4*>(a.cur);
-    uint4* __restrict__ nxt = reinterpret_cast<uint4*>(a.nxt);
-
-    if (blockIdx.x == 0 && threadIdx.x == 0) a.best[(a.best_slot + 1u) & 3u] = 0ull;
-
-    const uint32_t gwarp = blockIdx.x * WARPS + w, nwarps = gridDim.x * WARPS;
-    const uint32_t total = (a.n + 31u) >> 5;  // warp iterations in the population
-    const uint32_t iters = gwarp < total ? (total - gwarp + nwarps - 1u) / nwarps : 0u;
-    unsigned long long key = 0ull;
-
-    // copy both parent rows of the 16 children of half `h` into stage h
-    auto issue_half = [&](uint32_t p1, uint32_t p2, uint32_t h) {
-        unsigned char* st = my + h * STAGE;
-#pragma unroll
-        for (uint32_t t = 0; t < HT; ++t) {
-            const uint32_t c = (h * HT + t) * CPT + grp;  // child slot 0..31 of the iteration
-            const uint32_t q1 = __shfl_sync(0xFFFFFFFFu, p1, c);
-            const uint32_t q2 = __shfl_sync(0xFFFFFFFFu, p2, c);
-            if (in_row) {
-                const uint32_t slot = (t * CPT + grp) * 2u;  // row slot inside the stage
-                cp_async_16(st + (slot + 0u) * ROW + gl * 16u, cur + (size_t)q1 * nblk + gl);
-                cp_async_16(st + (slot + 1u) * ROW + gl * 16u, cur + (size_t)q2 * nblk + gl);
-            }
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-    auto resolve = [&](const SelDraw& d, uint32_t it, uint32_t& p1, uint32_t& p2) {
-        const uint32_t mine = (gwarp + it * nwarps) * 32u + lane;
-        p1 = d.s0 < d.s1 ? d.c1 : d.c0;  // src/pga.cu:286-290
-        p2 = d.s2 < d.s3 ? d.c3 : d.c2;
-        if (a.sel && mine < a.n) { a.sel[2 * (size_t)mine] = (int32_t)p1; a.sel[2 * (size_t)mine + 1] = (int32_t)p2; }
-    };
-
-    float my_score = 0.f;
-    uint32_t mut_idx0 = 0, mut_val0 = 0, any0 = 0;
-    // crossover, mutation and scoring of half `h` of iteration `it`, from stage h
-    auto consume_half = [&](uint32_t it, uint32_t h) {
-        const uint32_t cbase = (gwarp + it * nwarps) * 32u;
-        const unsigned char* st = my + h * STAGE;
-#pragma unroll
-        for (uint32_t t = 0; t < HT; ++t) {
-            const uint32_t tile = h * HT + t;
-            const uint32_t c = tile * CPT + grp;
-            const uint32_t child = cbase + c;
-            uint32_t c_idx = 0, c_val = 0;
-            if (any0) {  // warp-uniform; 72 % of iterations have no mutation at all
-                c_idx = __shfl_sync(0xFFFFFFFFu, mut_idx0, c);
-                c_val = __shfl_sync(0xFFFFFFFFu, mut_val0, c);
-            }
-            const bool c_on = (any0 >> c) & 1u;
-            const uint32_t c_blk = ENC == ENC_BITS ? (c_idx >> 7) : (c_idx >> 2);
-            float facc = 0.f;
-            uint32_t iacc = 0;
-            if (in_row) {
-                const uint32_t slot = (t * CPT + grp) * 2u;
-                const uint4 xx = *reinterpret_cast<const uint4*>(st + (slot + 0u) * ROW + gl * 16u);
-                const uint4 yy = *reinterpret_cast<const uint4*>(st + (slot + 1u) * ROW + gl * 16u);
-                uint4 o;
-                if (ENC == ENC_BITS) {
-                    const uint4 m = draw_block(a.draw, STREAM_MASK, child, gl);
-                    o.x = (xx.x & m.x) | (yy.x & ~m.x);
-                    o.y = (xx.y & m.y) | (yy.y & ~m.y);
-                    o.z = (xx.z & m.z) | (yy.z & ~m.z);
-                    o.w = (xx.w & m.w) | (yy.w & ~m.w);
-                } else {
-                    const uint4 r = draw_block(a.draw, STREAM_ROW, child, gl);
-                    o.x = draw_above_half(r.x) ? xx.x : yy.x;  // src/pga.cu:137-141
-                    o.y = draw_above_half(r.y) ? xx.y : yy.y;
-                    o.z = draw_above_half(r.z) ? xx.z : yy.z;
-                    o.w = draw_above_half(r.w) ? xx.w : yy.w;
-                }
-                if (c_on && c_blk == gl) {  // src/pga.cu:127-133; rare
-                    if (ENC == ENC_BITS) {
-                        const uint32_t word = (c_idx >> 5) & 3u, bit = 1u << (c_idx & 31u);
-                        uint32_t* cw = word == 0 ? &o.x : word == 1 ? &o.y : word == 2 ? &o.z : &o.w;
-                        *cw = c_val ? (*cw | bit) : (*cw & ~bit);
-                    } else {
-                        const uint32_t e = c_idx & 3u;
-                        if (e == 0) o.x = c_val; else if (e == 1) o.y = c_val; else if (e == 2) o.z = c_val; else o.w = c_val;
-                    }
-                }
-                if (ENC == ENC_BITS) {
-                    iacc = __popc(o.x) + __popc(o.y) + __popc(o.z) + __popc(o.w);
-                } else {
-                    const uint32_t j = 4u * gl;
-                    if (EXACT || j + 0 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(o.x));
-                    if (EXACT || j + 1 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(o.y));
-                    if (EXACT || j + 2 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(o.z));
-                    if (EXACT || j + 3 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(o.w));
-                }
-                if (child < a.n) store_row_block(nxt + (size_t)child * nblk + gl, o);
-            }
-            float s;
-            if (ENC == ENC_BITS) {
-#pragma unroll
-                for (uint32_t off = G >> 1; off >= 1u; off >>= 1) iacc += __shfl_xor_sync(0xFFFFFFFFu, iacc, off);
-                s = __uint2float_rn(iacc);
-            } else {
-#pragma unroll
-                for (uint32_t off = G >> 1; off >= 1u; off >>= 1)
-                    facc = __fadd_rn(facc, __shfl_xor_sync(0xFFFFFFFFu, facc, off));
-                s = obj_finalize<OBJ>(facc, a.len);
-            }
-            const float v = __shfl_sync(0xFFFFFFFFu, s, (lane & (CPT - 1u)) << LOGG);
-            if ((lane >> (5 - LOGG)) == tile) my_score = v;
-        }
-    };
-
-    SelDraw dn;  // the iteration after the current one: its score gathers are in flight
-    uint32_t p1n = 0, p2n = 0, mut_idx1 = 0, mut_val1 = 0, any1 = 0;
-    if (iters > 0) {
-        dn = sel_begin<ENC>(a, gwarp * 32u + lane);
-        resolve(dn, 0, p1n, p2n);
-        mut_idx0 = dn.m_idx; mut_val0 = dn.m_val; any0 = __ballot_sync(0xFFFFFFFFu, dn.m_on);
-        issue_half(p1n, p2n, 0);
-        issue_half(p1n, p2n, 1);
-        if (iters > 1) dn = sel_begin<ENC>(a, (gwarp + nwarps) * 32u + lane);
-    }
-
-    for (uint32_t it = 0; it < iters; ++it) {
-        const bool more = it + 1u < iters;
-        // half 0
-        asm volatile("cp.async.wait_group 1;" ::: "memory");
-        __syncwarp();
-        consume_half(it, 0);
-        __syncwarp();
-        if (more) {
-            resolve(dn, it + 1u, p1n, p2n);
-            mut_idx1 = dn.m_idx; mut_val1 = dn.m_val; any1 = __ballot_sync(0xFFFFFFFFu, dn.m_on);
-            issue_half(p1n, p2n, 0);
-        } else {
-            asm volatile("cp.async.commit_group;" ::: "memory");  // keep the group count uniform
-        }
-        // half 1
-        asm volatile("cp.async.wait_group 1;" ::: "memory");
-        __syncwarp();
-        consume_half(it, 1);
-        __syncwarp();
-        if (more) issue_half(p1n, p2n, 1);
-        else asm volatile("cp.async.commit_group;" ::: "memory");
-
-        const uint32_t mine = (gwarp + it * nwarps) * 32u + lane;
-        if (mine < a.n) {
-            a.score_out[mine] = my_score;
-            const unsigned long long k = best_key(my_score, mine);
-            key = k > key ? k : key;
-        }
-        mut_idx0 = mut_idx1; mut_val0 = mut_val1; any0 = any1;
-        if (it + 2u < iters) dn = sel_begin<ENC>(a, (gwarp + (it + 2u) * nwarps) * 32u + lane);
-    }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    block_best_commit(key, a.best + a.best_slot, warp_best);
-}
-
 // ---- population set-up (src/pga.cu:81-86, :116-117): genes := rand row of epoch 0 ----
 template <int ENC>
 __global__ void init_population(uint32_t* rows, uint32_t n, uint32_t len, uint32_t stride, DrawCtx d)
@@ -866,23 +652,11 @@ __global__ void best_of_slots(const BestSlots s, float* out)
 // ---- top-k radix select ------------------------------------------------------------
 //
 // Picks the k best (or k worst) individuals under the engine's total order and
-// lists them in ascending index order.  Four 8-bit passes over the 32-bit order
-// key find the k-th key T; a stable compaction then takes every key beyond T and
-// as many keys equal to T as are still needed (lowest indices first for "best",
-// highest first for "worst").  Histogram updates are aggregated per warp with
-// __match_any_sync before they touch shared memory.
-struct TopkState {
-    uint32_t hist[256];
-    uint32_t prefix;     // digits fixed so far
-    uint32_t mask;       // which bits of `prefix` are fixed
-    uint32_t remaining;  // rank still to find inside the prefix bucket
-    uint32_t threshold;  // final: the k-th key
-    uint32_t need_eq;    // final: how many keys == threshold are taken
-    uint32_t total_eq;   // final: how many keys == threshold exist
-    uint32_t total_gt;   // final: how many keys  > threshold exist
-    uint32_t pad;
-};
-
+// lists them in ascending index order.  Radix passes over the 32-bit order key find
+// the k-th key T; a stable compaction then takes every key beyond T and as many keys
+// equal to T as are still needed (lowest indices first for "best", highest first for
+// "worst").  Histogram updates are aggregated per warp with __match_any_sync before
+// they touch shared memory.
 #define TOPK_BLOCK 256u
 #define TOPK_ROUNDS 8u
 #define TOPK_CHUNK (TOPK_BLOCK * TOPK_ROUNDS)
@@ -893,187 +667,9 @@ __device__ __forceinline__ uint32_t select_key(float s, int worst)
     return worst ? ~k : k;
 }
 
-__global__ void topk_begin(TopkState* st, uint32_t k)
-{
-    const uint32_t t = threadIdx.x;
-    if (t < 256u) st->hist[t] = 0u;
-    if (t == 0) {
-        st->prefix = 0u; st->mask = 0u; st->remaining = k;
-        st->threshold = 0u; st->need_eq = 0u; st->total_eq = 0u; st->total_gt = 0u;
-    }
-}
-
-__global__ void __launch_bounds__(256) topk_histogram(const float* __restrict__ score, uint32_t n, int worst, uint32_t shift,
-                                                      TopkState* st)
-{
-    __shared__ uint32_t h[256];
-    h[threadIdx.x] = 0u;
-    __syncthreads();
-    const uint32_t prefix = st->prefix, mask = st->mask;
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint64_t span = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t base = (uint64_t)blockIdx.x * blockDim.x; base < n; base += span) {
-        const uint64_t i = base + threadIdx.x;
-        const bool in = i < n;
-        uint32_t key = 0u;
-        bool hit = false;
-        if (in) {
-            key = select_key(__ldg(score + i), worst);
-            hit = (key & mask) == prefix;
-        }
-        const uint32_t digit = (key >> shift) & 255u;
-        // one shared-memory atomic per distinct digit in the warp
-        const uint32_t voters = __ballot_sync(0xFFFFFFFFu, hit);
-        if (hit) {
-            const uint32_t peers = __match_any_sync(voters, digit);
-            if ((peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&h[digit], (uint32_t)__popc(peers));
-        }
-    }
-    __syncthreads();
-    if (h[threadIdx.x]) atomicAdd(&st->hist[threadIdx.x], h[threadIdx.x]);
-}
-
-// one block: walk the digits from the top until the cumulative count reaches `remaining`
-__global__ void topk_pick(TopkState* st, uint32_t shift)
-{
-    __shared__ uint32_t h[256];
-    const uint32_t t = threadIdx.x;
-    h[t] = st->hist[t];
-    __syncthreads();
-    if (t == 0) {
-        uint32_t rem = st->remaining, above = 0u, d = 255u;
-        for (;; --d) {
-            if (above + h[d] >= rem || d == 0u) break;
-            above += h[d];
-        }
-        st->remaining = rem - above;
-        st->prefix |= d << shift;
-        st->mask |= 255u << shift;
-        st->total_gt += above;
-        if (shift == 0u) {
-            st->threshold = st->prefix;
-            st->need_eq = rem - above;
-            st->total_eq = h[d];
-        }
-    }
-    __syncthreads();
-    st->hist[t] = 0u;
-}
-
-__global__ void __launch_bounds__(256) topk_count(const float* __restrict__ score, uint32_t n, int worst, const TopkState* st,
-                                                  uint32_t* block_gt, uint32_t* block_eq)
-{
-    __shared__ uint32_t s_gt, s_eq;
-    if (threadIdx.x == 0) { s_gt = 0u; s_eq = 0u; }
-    __syncthreads();
-    const uint32_t T = st->threshold;
-    uint32_t gt = 0u, eq = 0u;
-    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
-    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
-        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
-        if (i < n) {
-            const uint32_t key = select_key(__ldg(score + i), worst);
-            gt += key > T;
-            eq += key == T;
-        }
-    }
-    for (int off = 16; off >= 1; off >>= 1) {
-        gt += __shfl_xor_sync(0xFFFFFFFFu, gt, off);
-        eq += __shfl_xor_sync(0xFFFFFFFFu, eq, off);
-    }
-    if ((threadIdx.x & 31u) == 0u) { atomicAdd(&s_gt, gt); atomicAdd(&s_eq, eq); }
-    __syncthreads();
-    if (threadIdx.x == 0) { block_gt[blockIdx.x] = s_gt; block_eq[blockIdx.x] = s_eq; }
-}
-
-// one block: exclusive scans of the per-block counts, in place
-__global__ void __launch_bounds__(1024) topk_scan(uint32_t* block_gt, uint32_t* block_eq, uint32_t nb)
-{
-    __shared__ uint32_t wsum[2][32];
-    __shared__ uint32_t carry[2];
-    const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
-    if (t == 0) { carry[0] = 0u; carry[1] = 0u; }
-    __syncthreads();
-    for (uint32_t base = 0; base < nb; base += 1024u) {
-        const uint32_t i = base + t;
-        uint32_t v[2] = { i < nb ? block_gt[i] : 0u, i < nb ? block_eq[i] : 0u };
-        uint32_t inc[2] = { v[0], v[1] };
-        for (int q = 0; q < 2; ++q) {
-            for (int off = 1; off < 32; off <<= 1) {
-                const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc[q], off);
-                if ((int)lane >= off) inc[q] += o;
-            }
-            if (lane == 31u) wsum[q][warp] = inc[q];
-        }
-        __syncthreads();
-        if (warp == 0) {
-            for (int q = 0; q < 2; ++q) {
-                uint32_t w = wsum[q][lane], wi = w;
-                for (int off = 1; off < 32; off <<= 1) {
-                    const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, wi, off);
-                    if ((int)lane >= off) wi += o;
-                }
-                wsum[q][lane] = wi - w;  // exclusive
-            }
-        }
-        __syncthreads();
-        uint32_t tot[2];
-        for (int q = 0; q < 2; ++q) {
-            const uint32_t excl = carry[q] + wsum[q][warp] + inc[q] - v[q];
-            if (i < nb) (q == 0 ? block_gt : block_eq)[i] = excl;
-            tot[q] = excl + v[q];
-        }
-        __syncthreads();
-        if (t == 1023u) { carry[0] = tot[0]; carry[1] = tot[1]; }
-        __syncthreads();
-    }
-}
-
-__global__ void __launch_bounds__(256) topk_emit(const float* __restrict__ score, uint32_t n, int worst, const TopkState* st,
-                                                 const uint32_t* block_gt, const uint32_t* block_eq, uint32_t* out_idx)
-{
-    __shared__ uint32_t w_gt[8], w_eq[8];
-    __shared__ uint32_t run_gt, run_eq;
-    const uint32_t T = st->threshold, need = st->need_eq, total_eq = st->total_eq;
-    // "best": the first `need` equal keys by index; "worst": the last `need`
-    const uint32_t eq_lo = worst ? total_eq - need : 0u, eq_hi = worst ? total_eq : need;
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) { run_gt = block_gt[blockIdx.x]; run_eq = block_eq[blockIdx.x]; }
-    __syncthreads();
-    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
-    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
-        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
-        bool gt = false, eq = false;
-        if (i < n) {
-            const uint32_t key = select_key(__ldg(score + i), worst);
-            gt = key > T;
-            eq = key == T;
-        }
-        const uint32_t bg = __ballot_sync(0xFFFFFFFFu, gt), be = __ballot_sync(0xFFFFFFFFu, eq);
-        const uint32_t lt_mask = (1u << lane) - 1u;
-        if (lane == 0) { w_gt[warp] = __popc(bg); w_eq[warp] = __popc(be); }
-        __syncthreads();
-        uint32_t gt_before = run_gt + __popc(bg & lt_mask), eq_before = run_eq + __popc(be & lt_mask);
-        for (uint32_t w = 0; w < warp; ++w) { gt_before += w_gt[w]; eq_before += w_eq[w]; }
-        // position among the selected = selected elements with a lower index
-        const uint32_t eq_sel_before = eq_before <= eq_lo ? 0u : (eq_before >= eq_hi ? eq_hi - eq_lo : eq_before - eq_lo);
-        if (gt) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
-        else if (eq && eq_before >= eq_lo && eq_before < eq_hi) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            uint32_t g = 0u, e = 0u;
-            for (uint32_t w = 0; w < 8u; ++w) { g += w_gt[w]; e += w_eq[w]; }
-            run_gt += g; run_eq += e;
-        }
-        __syncthreads();
-    }
-}
-
-// ---- top-k radix select, short form ---------------------------------------------------
+// ---- the selection in five launches ----------------------------------------------------
 //
-// The same selection in 5 launches instead of 12 (a migration is latency-bound: a
-// dozen dependent 3-us launches cost more than the work inside them).  Three radix
-// passes of 11 + 11 + 10 bits; the last block to finish a pass (ticket counter after
+// Three radix passes of 11 + 11 + 10 bits; the last block to finish a pass (ticket counter after
 // a __threadfence) picks the digit, so no separate pick launch; the last block of the
 // count pass scans the per-block counts.  State is left clean for the next call.
 #define TOPK2_BINS 2048u
@@ -1117,36 +713,40 @@ __device__ __forceinline__ void pick_digit(const uint32_t* h, uint32_t nbins, ui
 }
 
 template <uint32_t SHIFT, uint32_t BITS>
-__global__ void __launch_bounds__(256) topk2_histogram(const float* __restrict__ score, uint32_t n, int worst, uint32_t k, TopkState2* st)
+__global__ void __launch_bounds__(256) topk2_histogram(const float* __restrict__ score, uint32_t n, int worst, uint32_t k, TopkState2* st, uint32_t nb)
 {
     constexpr uint32_t NBINS = 1u << BITS;
     __shared__ uint32_t h[TOPK2_BINS];
     __shared__ uint32_t scratch[16];
     __shared__ uint32_t is_last, s_digit, s_above;
-    // one 2048-score chunk per block; all eight loads of a thread are issued before the
-    // first is used (the ballots below would otherwise serialise eight round trips)
-    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
-    float v[TOPK_ROUNDS];
-#pragma unroll
-    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
-        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
-        v[r] = i < n ? __ldg(score + i) : 0.f;
-    }
     for (uint32_t i = threadIdx.x; i < NBINS; i += 256u) h[i] = 0u;
     __syncthreads();
     const bool first = SHIFT + BITS == 32u;  // the first pass starts from an empty prefix
     const uint32_t prefix = first ? 0u : st->prefix, mask = first ? 0u : st->mask;
     const uint32_t lane = threadIdx.x & 31u;
+    // 2048-score chunks, grid-stride: the grid may be far smaller than the number of chunks
+    // (a ranking that runs beside a generation kernel only gets the SMs that kernel left free).
+    // All eight loads of a thread are issued before the first is used (the ballots below
+    // would otherwise serialise eight round trips).
+    for (uint32_t chunk = blockIdx.x; chunk < nb; chunk += gridDim.x) {
+        const uint64_t base = (uint64_t)chunk * TOPK_CHUNK;
+        float v[TOPK_ROUNDS];
 #pragma unroll
-    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
-        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
-        const uint32_t key = select_key(v[r], worst);
-        const bool hit = i < n && (key & mask) == prefix;
-        const uint32_t digit = (key >> SHIFT) & (NBINS - 1u);
-        const uint32_t voters = __ballot_sync(0xFFFFFFFFu, hit);
-        if (hit) {  // one shared-memory atomic per distinct digit in the warp
-            const uint32_t peers = __match_any_sync(voters, digit);
-            if ((peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&h[digit], (uint32_t)__popc(peers));
+        for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+            const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+            v[r] = i < n ? __ldg(score + i) : 0.f;
+        }
+#pragma unroll
+        for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+            const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+            const uint32_t key = select_key(v[r], worst);
+            const bool hit = i < n && (key & mask) == prefix;
+            const uint32_t digit = (key >> SHIFT) & (NBINS - 1u);
+            const uint32_t voters = __ballot_sync(0xFFFFFFFFu, hit);
+            if (hit) {  // one shared-memory atomic per distinct digit in the warp
+                const uint32_t peers = __match_any_sync(voters, digit);
+                if ((peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&h[digit], (uint32_t)__popc(peers));
+            }
         }
     }
     __syncthreads();
@@ -1188,33 +788,38 @@ __global__ void __launch_bounds__(256) topk2_count_scan(const float* __restrict_
     __shared__ uint32_t s_gt, s_eq, is_last;
     __shared__ uint32_t wsum[2][8];
     __shared__ uint32_t carry[2];
-    if (threadIdx.x == 0) { s_gt = 0u; s_eq = 0u; }
-    __syncthreads();
-    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK;
-    float v[TOPK_ROUNDS];
-#pragma unroll
-    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
-        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
-        v[r] = i < n ? __ldg(score + i) : 0.f;
-    }
     const uint32_t T = st->threshold;
-    uint32_t gt = 0u, eq = 0u;
+    for (uint32_t chunk = blockIdx.x; chunk < nb; chunk += gridDim.x) {  // counts are per chunk, whatever the grid
+        if (threadIdx.x == 0) { s_gt = 0u; s_eq = 0u; }
+        __syncthreads();
+        const uint64_t base = (uint64_t)chunk * TOPK_CHUNK;
+        float v[TOPK_ROUNDS];
 #pragma unroll
-    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
-        const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
-        const uint32_t key = select_key(v[r], worst);
-        gt += i < n && key > T;
-        eq += i < n && key == T;
+        for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+            const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+            v[r] = i < n ? __ldg(score + i) : 0.f;
+        }
+        uint32_t gt = 0u, eq = 0u;
+#pragma unroll
+        for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+            const uint64_t i = base + r * TOPK_BLOCK + threadIdx.x;
+            const uint32_t key = select_key(v[r], worst);
+            gt += i < n && key > T;
+            eq += i < n && key == T;
+        }
+        for (int off = 16; off >= 1; off >>= 1) {
+            gt += __shfl_xor_sync(0xFFFFFFFFu, gt, off);
+            eq += __shfl_xor_sync(0xFFFFFFFFu, eq, off);
+        }
+        if ((threadIdx.x & 31u) == 0u) { atomicAdd(&s_gt, gt); atomicAdd(&s_eq, eq); }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            block_gt[chunk] = s_gt;
+            block_eq[chunk] = s_eq;
+        }
+        __syncthreads();
     }
-    for (int off = 16; off >= 1; off >>= 1) {
-        gt += __shfl_xor_sync(0xFFFFFFFFu, gt, off);
-        eq += __shfl_xor_sync(0xFFFFFFFFu, eq, off);
-    }
-    if ((threadIdx.x & 31u) == 0u) { atomicAdd(&s_gt, gt); atomicAdd(&s_eq, eq); }
-    __syncthreads();
     if (threadIdx.x == 0) {
-        block_gt[blockIdx.x] = s_gt;
-        block_eq[blockIdx.x] = s_eq;
         __threadfence();
         is_last = atomicAdd(&st->ticket, 1u) == gridDim.x - 1u;
     }
@@ -1252,48 +857,61 @@ __global__ void __launch_bounds__(256) topk2_count_scan(const float* __restrict_
 }
 
 __global__ void __launch_bounds__(256) topk2_emit(const float* __restrict__ score, uint32_t n, int worst, const TopkState2* st,
-                                                  const uint32_t* block_gt, const uint32_t* block_eq, uint32_t* out_idx)
+                                                  const uint32_t* block_gt, const uint32_t* block_eq, uint32_t* out_idx, uint32_t nb)
 {
-    // Each warp owns 256 CONSECUTIVE scores of the block's chunk (8 sub-rounds of 32), so
-    // index order is warp-major and the block needs one barrier: warp totals -> prefix.
+    // Each warp owns 256 CONSECUTIVE scores of a chunk (8 sub-rounds of 32), so index
+    // order is warp-major and a chunk needs one barrier: warp totals -> prefix.
     __shared__ uint32_t w_gt[8], w_eq[8];
     const uint32_t T = st->threshold, need = st->need_eq, total_eq = st->total_eq;
     // "best": the first `need` equal keys by index; "worst": the last `need`
     const uint32_t eq_lo = worst ? total_eq - need : 0u, eq_hi = worst ? total_eq : need;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint64_t base = (uint64_t)blockIdx.x * TOPK_CHUNK + warp * 256u;
-    float v[TOPK_ROUNDS];
+    for (uint32_t chunk = blockIdx.x; chunk < nb; chunk += gridDim.x) {
+        const uint64_t base = (uint64_t)chunk * TOPK_CHUNK + warp * 256u;
+        float v[TOPK_ROUNDS];
 #pragma unroll
-    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
-        const uint64_t i = base + r * 32u + lane;
-        v[r] = i < n ? __ldg(score + i) : 0.f;
+        for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+            const uint64_t i = base + r * 32u + lane;
+            v[r] = i < n ? __ldg(score + i) : 0.f;
+        }
+        uint32_t bg[TOPK_ROUNDS], be[TOPK_ROUNDS], tot_g = 0u, tot_e = 0u;
+#pragma unroll
+        for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+            const uint64_t i = base + r * 32u + lane;
+            const uint32_t key = select_key(v[r], worst);
+            bg[r] = __ballot_sync(0xFFFFFFFFu, i < n && key > T);
+            be[r] = __ballot_sync(0xFFFFFFFFu, i < n && key == T);
+            tot_g += __popc(bg[r]);
+            tot_e += __popc(be[r]);
+        }
+        if (lane == 0) { w_gt[warp] = tot_g; w_eq[warp] = tot_e; }
+        __syncthreads();
+        uint32_t run_g = block_gt[chunk], run_e = block_eq[chunk];
+        for (uint32_t w2 = 0; w2 < warp; ++w2) { run_g += w_gt[w2]; run_e += w_eq[w2]; }
+        const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+        for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
+            const uint64_t i = base + r * 32u + lane;
+            const bool gt = (bg[r] >> lane) & 1u, eq = (be[r] >> lane) & 1u;
+            const uint32_t gt_before = run_g + __popc(bg[r] & lt_mask), eq_before = run_e + __popc(be[r] & lt_mask);
+            // position among the selected = selected elements with a lower index
+            const uint32_t eq_sel_before = eq_before <= eq_lo ? 0u : (eq_before >= eq_hi ? eq_hi - eq_lo : eq_before - eq_lo);
+            if (gt) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
+            else if (eq && eq_before >= eq_lo && eq_before < eq_hi) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
+            run_g += __popc(bg[r]);
+            run_e += __popc(be[r]);
+        }
+        __syncthreads();  // the warp totals are rewritten for the next chunk
     }
-    uint32_t bg[TOPK_ROUNDS], be[TOPK_ROUNDS], tot_g = 0u, tot_e = 0u;
-#pragma unroll
-    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
-        const uint64_t i = base + r * 32u + lane;
-        const uint32_t key = select_key(v[r], worst);
-        bg[r] = __ballot_sync(0xFFFFFFFFu, i < n && key > T);
-        be[r] = __ballot_sync(0xFFFFFFFFu, i < n && key == T);
-        tot_g += __popc(bg[r]);
-        tot_e += __popc(be[r]);
-    }
-    if (lane == 0) { w_gt[warp] = tot_g; w_eq[warp] = tot_e; }
-    __syncthreads();
-    uint32_t run_g = block_gt[blockIdx.x], run_e = block_eq[blockIdx.x];
-    for (uint32_t w2 = 0; w2 < warp; ++w2) { run_g += w_gt[w2]; run_e += w_eq[w2]; }
-    const uint32_t lt_mask = (1u << lane) - 1u;
-#pragma unroll
-    for (uint32_t r = 0; r < TOPK_ROUNDS; ++r) {
-        const uint64_t i = base + r * 32u + lane;
-        const bool gt = (bg[r] >> lane) & 1u, eq = (be[r] >> lane) & 1u;
-        const uint32_t gt_before = run_g + __popc(bg[r] & lt_mask), eq_before = run_e + __popc(be[r] & lt_mask);
-        // position among the selected = selected elements with a lower index
-        const uint32_t eq_sel_before = eq_before <= eq_lo ? 0u : (eq_before >= eq_hi ? eq_hi - eq_lo : eq_before - eq_lo);
-        if (gt) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
-        else if (eq && eq_before >= eq_lo && eq_before < eq_hi) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
-        run_g += __popc(bg[r]);
-        run_e += __popc(be[r]);
+}
+
+// state of a ranking that starts from memory of unknown content (pgax_select_top_noalloc)
+__global__ void topk2_reset(TopkState2* st)
+{
+    for (uint32_t i = threadIdx.x; i < TOPK2_BINS; i += blockDim.x) st->hist[i] = 0u;
+    if (threadIdx.x == 0) {
+        st->prefix = 0u; st->mask = 0u; st->remaining = 0u;
+        st->threshold = 0u; st->need_eq = 0u; st->total_eq = 0u; st->total_gt = 0u; st->ticket = 0u;
     }
 }
 
