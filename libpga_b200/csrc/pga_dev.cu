@@ -22,7 +22,6 @@
 #include "../../include/pga_b200.h"
 #include "pga_dev.h"
 #include "pga_kernels.cuh"
-#include "pga_kernel_sorted.cuh"
 
 using namespace pgak;
 
@@ -53,8 +52,6 @@ struct pgadev_ctx {
     int no_hook_split;            // $PGA_NO_HOOK_SPLIT=1: generations with hooks are always one launch
     int no_coop;                  // $PGA_NO_COOP=1: rank with the 5-launch select instead of the cooperative kernel
     uint32_t reserve_now;         // SMs' worth of blocks the current launch leaves free (pgadev_step.reserve_sms)
-    int sorted;                   // $PGA_SORTED: long rows visited in first-parent order (0 = off, 1 = on, 2 = alternative occupancy)
-    uint32_t side_blocks;         // $PGA_SIDE_BLOCKS: grid of a ranking that runs beside a generation (default 64)
     // early-stop check (pgax_set_target): best score of the local populations
     float* check_dev;
     float* check_host;  // pinned
@@ -77,8 +74,9 @@ struct pgadev_pop {
     int capture;
     // ranking scratch
     TopkState2* topk[2];  // one set per index list: emigrants may be ranked on the side stream
-    TopkCoop* coop[2];
+    TopkOne* coop[2];
     unsigned long long coop_arrivals[2];  // barrier arrivals consumed so far by the cooperative select
+    uint32_t coop_calls[2];               // its histograms alternate between two copies
     uint32_t *blk_gt[2], *blk_eq[2];
     uint32_t nb;
     uint32_t* idx[2];
@@ -90,10 +88,6 @@ struct pgadev_pop {
     // migration boxes
     uint32_t *outbox, *inbox;
     uint64_t box_cap;
-    // first-parent-ordered generation (pga_kernel_sorted.cuh): pairs, counts/offsets, block offsets, records
-    uint2* srt_pair;
-    uint32_t *srt_count, *srt_block;
-    uint4* srt_rec;
     // host <-> device staging for padded rows
     uint32_t* stage;
     size_t stage_bytes;
@@ -151,8 +145,6 @@ extern "C" pgadev_ctx* pgadev_ctx_create(void)
     c->force_generic = (e = getenv("PGA_FORCE_GENERIC")) ? atoi(e) : 0;
     c->no_hook_split = (e = getenv("PGA_NO_HOOK_SPLIT")) ? atoi(e) : 0;
     c->no_coop = (e = getenv("PGA_NO_COOP")) ? atoi(e) : 0;
-    c->sorted = (e = getenv("PGA_SORTED")) ? atoi(e) : 0;
-    c->side_blocks = (e = getenv("PGA_SIDE_BLOCKS")) && atoi(e) > 0 ? (uint32_t)atoi(e) : 64u;
     const char* stack = getenv("PGA_STACK_BYTES");  // device stack for deep user hooks
     if (stack && atoi(stack) > 0) CCE(cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(stack)));
     return c;
@@ -196,6 +188,50 @@ extern "C" float pgadev_timer_ms(pgadev_ctx* c)
     CCE(cudaEventSynchronize(c->t1));
     CCE(cudaEventElapsedTime(&ms, c->t0, c->t1));
     return ms;
+}
+
+// ---- $PGA_TRACE=1: where the time of a run goes -------------------------------------------------------
+// Events on the main stream at named points of the generation / migration schedule; the gaps
+// between consecutive marks are summed per (from, to) pair and printed to stderr when the run
+// ends.  Costs nothing when the variable is not set.
+#define TRACE_MAX 8192
+static struct {
+    int enabled, init;
+    cudaEvent_t ev[TRACE_MAX];
+    const char* label[TRACE_MAX];
+    int count;
+} g_trace;
+
+extern "C" void pgadev_trace_mark(pgadev_ctx* c, const char* label)
+{
+    if (!g_trace.init) {
+        const char* e = getenv("PGA_TRACE");
+        g_trace.enabled = e && atoi(e) > 0;
+        g_trace.init = 1;
+    }
+    if (!g_trace.enabled || g_trace.count >= TRACE_MAX) return;
+    if (!g_trace.ev[g_trace.count]) CCE(cudaEventCreate(&g_trace.ev[g_trace.count]));
+    CCE(cudaEventRecord(g_trace.ev[g_trace.count], c->stream));
+    g_trace.label[g_trace.count++] = label;
+}
+
+extern "C" void pgadev_trace_report(pgadev_ctx* c)
+{
+    if (!g_trace.enabled || g_trace.count < 2) { g_trace.count = 0; return; }
+    CCE(cudaStreamSynchronize(c->stream));
+    struct { const char *a, *b; double ms; int n; } agg[64];
+    int na = 0;
+    for (int i = 1; i < g_trace.count; ++i) {
+        float ms = 0.f;
+        CCE(cudaEventElapsedTime(&ms, g_trace.ev[i - 1], g_trace.ev[i]));
+        int j = 0;
+        while (j < na && !(agg[j].a == g_trace.label[i - 1] && agg[j].b == g_trace.label[i])) ++j;
+        if (j == na) { if (na == 64) continue; agg[na].a = g_trace.label[i - 1]; agg[na].b = g_trace.label[i]; agg[na].ms = 0; agg[na].n = 0; ++na; }
+        agg[j].ms += ms; agg[j].n += 1;
+    }
+    for (int j = 0; j < na; ++j)
+        fprintf(stderr, "pga-trace: %-22s -> %-22s %6d x %9.2f us\n", agg[j].a, agg[j].b, agg[j].n, 1e3 * agg[j].ms / agg[j].n);
+    g_trace.count = 0;
 }
 
 // ---- populations ------------------------------------------------------------------
@@ -254,10 +290,6 @@ extern "C" void pgadev_pop_destroy(pgadev_ctx* c, pgadev_pop* p)
     if (p->outbox) CCE(cudaFree(p->outbox));
     if (p->inbox) CCE(cudaFree(p->inbox));
     if (p->stage) CCE(cudaFree(p->stage));
-    if (p->srt_pair) CCE(cudaFree(p->srt_pair));
-    if (p->srt_count) CCE(cudaFree(p->srt_count));
-    if (p->srt_block) CCE(cudaFree(p->srt_block));
-    if (p->srt_rec) CCE(cudaFree(p->srt_rec));
     free(p);
 }
 
@@ -402,13 +434,18 @@ template <int ENC, int OBJ, int LOGG, int NB, bool EXACT>
 static int launch_tiled_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
 {
     constexpr int TB = TiledShape<ENC, LOGG, NB>::TB, MINB = TiledShape<ENC, LOGG, NB>::MINB;
-    constexpr uint32_t THREADS = 256u * MINB;
-    // exactly one resident wave, one block per SM (a partial second wave costs a full kernel
-    // tail), minus the SMs held back so that side-stream work can run beside this launch
-    const uint32_t per_sm = c->fast_blocks_per_sm_set ? c->fast_blocks_per_sm : 1u;
-    const uint32_t sms = (uint32_t)c->sm_count - (c->reserve_now < (uint32_t)c->sm_count / 2u ? c->reserve_now : (uint32_t)c->sm_count / 2u);
-    const uint32_t grid = grid_for(p->n, THREADS, sms * per_sm);
-    generation_fused_tiled<ENC, OBJ, LOGG, NB, TB, EXACT, MINB><<<grid, THREADS, 0, c->stream>>>(a);
+    // exactly one resident wave of 8 * MINB warps per SM (a partial second wave costs a full
+    // kernel tail).  While a migration is in flight the launch holds `reserve_now` SMs back
+    // and takes the one-block-per-SM form, which leaves those SMs empty for the side stream.
+    const uint32_t per_sm = c->fast_blocks_per_sm_set ? c->fast_blocks_per_sm : (uint32_t)MINB;
+    if (c->reserve_now == 0) {
+        const uint32_t grid = grid_for(p->n, 256, (uint32_t)c->sm_count * per_sm);
+        generation_fused_tiled<ENC, OBJ, LOGG, NB, TB, EXACT, MINB, false><<<grid, 256, 0, c->stream>>>(a);
+    } else {
+        const uint32_t sms = (uint32_t)c->sm_count - (c->reserve_now < (uint32_t)c->sm_count / 2u ? c->reserve_now : (uint32_t)c->sm_count / 2u);
+        const uint32_t grid = grid_for(p->n, 256u * MINB, sms);
+        generation_fused_tiled<ENC, OBJ, LOGG, NB, TB, EXACT, MINB, true><<<grid, 256 * MINB, 0, c->stream>>>(a);
+    }
     LAUNCH_CHECK(c);
     return 0;
 }
@@ -419,56 +456,6 @@ static int launch_tiled_inst(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
     // EXACT: every lane of a group owns exactly NB blocks and (f32) no gene is padding
     const bool exact = (p->stride >> 2) == (uint32_t)NB << LOGG && (ENC == ENC_BITS || p->len == p->stride);
     return exact ? launch_tiled_one<ENC, OBJ, LOGG, NB, true>(c, p, a) : launch_tiled_one<ENC, OBJ, LOGG, NB, false>(c, p, a);
-}
-
-// ---- long rows: children visited in first-parent order (pga_kernel_sorted.cuh) ---------------------
-template <int ENC, int OBJ, int NB, bool EXACT, int MINB>
-static int launch_sorted_one(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
-{
-    const uint32_t n = (uint32_t)p->n;
-    const uint32_t nbk = (n + SORTED_SCAN_CHUNK - 1u) / SORTED_SCAN_CHUNK;
-    if (!p->srt_rec) {
-        CCE(cudaMalloc((void**)&p->srt_pair, (size_t)n * sizeof(uint2)));
-        CCE(cudaMalloc((void**)&p->srt_count, (size_t)n * sizeof(uint32_t)));
-        CCE(cudaMalloc((void**)&p->srt_block, (size_t)(nbk + 1u) * sizeof(uint32_t)));
-        CCE(cudaMalloc((void**)&p->srt_rec, (size_t)n * sizeof(uint4)));
-    }
-    const uint32_t sms = (uint32_t)c->sm_count - (c->reserve_now < (uint32_t)c->sm_count / 2u ? c->reserve_now : (uint32_t)c->sm_count / 2u);
-    const uint32_t wide = grid_for(n, 256, sms * 8u);
-    CCE(cudaMemsetAsync(p->srt_count, 0, (size_t)n * sizeof(uint32_t), c->stream));
-    sorted_select<<<wide, 256, 0, c->stream>>>(a, p->srt_pair, p->srt_count);
-    LAUNCH_CHECK(c);
-    sorted_scan_local<<<nbk, SORTED_SCAN_BLOCK, 0, c->stream>>>(p->srt_count, n, p->srt_block);
-    LAUNCH_CHECK(c);
-    sorted_scan_totals<<<1, 1024, 0, c->stream>>>(p->srt_block, nbk);
-    LAUNCH_CHECK(c);
-    sorted_scatter<<<wide, 256, 0, c->stream>>>(p->srt_pair, n, p->srt_count, p->srt_block, p->srt_rec);
-    LAUNCH_CHECK(c);
-    GenArgs g = a;
-    g.sel = nullptr;  // sorted_select has written the capture
-    const uint32_t grid = grid_for((n + 31u) / 32u, 8u * MINB, sms);
-    generation_sorted<ENC, OBJ, NB, EXACT, MINB><<<grid, 256 * MINB, 0, c->stream>>>(g, p->srt_rec);
-    LAUNCH_CHECK(c);
-    return 0;
-}
-
-// rows of more than 256 bytes (32 lanes per child), up to four 16-byte blocks per lane; 1 = not applicable
-template <int ENC, int OBJ>
-static int launch_sorted(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a)
-{
-    const uint32_t nblk = p->stride >> 2;
-    if (!c->sorted || c->force_generic || p->group != 32u || nblk > 128u || p->n < 8192u) return 1;
-    const uint32_t NBr = (nblk + 31u) / 32u;
-    const bool exact = nblk == NBr * 32u && (ENC == ENC_BITS || p->len == p->stride);
-    const bool alt = c->sorted == 2;
-#define SRT(N, M) return exact ? launch_sorted_one<ENC, OBJ, N, true, M>(c, p, a) : launch_sorted_one<ENC, OBJ, N, false, M>(c, p, a)
-    switch (NBr) {
-        case 1: if (alt) SRT(1, 2); SRT(1, 3);
-        case 2: if (alt) SRT(2, 3); SRT(2, 2);
-        case 3: SRT(3, 2);
-        default: SRT(4, 1);
-    }
-#undef SRT
 }
 
 // Shapes with a compile-time tiling: G = min(32, pow2ceil(blocks)) lanes per child (the
@@ -512,9 +499,7 @@ template <int ENC, int OBJ>
 static int launch_fast_ph(pgadev_ctx* c, pgadev_pop* p, const GenArgs& a, uint32_t ph)
 {
     if (ph == PH_FUSED && a.tk == 2u) {  // the compile-time tilings are built for the reference's size-2 tournament
-        int rc = launch_sorted<ENC, OBJ>(c, p, a);
-        if (rc <= 0) return rc;
-        rc = launch_tiled<ENC, OBJ>(c, p, a);
+        int rc = launch_tiled<ENC, OBJ>(c, p, a);
         if (rc <= 0) return rc;
     }
     switch (ph) {
@@ -710,44 +695,48 @@ static void ensure_index_list(pgadev_ctx* c, pgadev_pop* p, int slot, uint64_t k
 
 static cudaStream_t work_stream(pgadev_ctx* c) { return c->route_side ? c->side : c->stream; }
 
-// The whole selection as one cooperative launch, when the population is small enough
-// for every block to be resident at once (E scores per thread, E = 8, 16 or 32).
+// The whole selection as one cooperative launch of one 1024-thread block per SM, when E scores
+// per thread (E = 8, 16 or 32) cover the population.
 template <int E>
 static bool select_top_coop_e(pgadev_ctx* c, pgadev_pop* p, uint32_t k, int worst, int slot, cudaStream_t s)
 {
     static int occupancy[MAX_DEVICES];  // per device ordinal; -1 = the kernel does not fit
     int blocks_per_sm = occupancy[c->device % MAX_DEVICES];
     if (blocks_per_sm == 0) {
-        CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, topk_select_coop<E>, 256, 0));
+        CCE(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, topk_select_coop<E>, (int)TOPK1_THREADS, 0));
         if (blocks_per_sm < 1) blocks_per_sm = -1;
         occupancy[c->device % MAX_DEVICES] = blocks_per_sm;
     }
     if (blocks_per_sm < 0) return false;
-    const uint64_t per_block = 256ull * E;
+    const uint64_t per_block = (uint64_t)TOPK1_THREADS * E;
     const uint64_t grid = (p->n + per_block - 1) / per_block;
-    if (grid > (uint64_t)blocks_per_sm * (uint64_t)c->sm_count) return false;
+    if (grid > (uint64_t)c->sm_count || grid > 160u) return false;
     if (!p->coop[slot]) {
-        CCE(cudaMalloc((void**)&p->coop[slot], sizeof(TopkCoop)));
-        CCE(cudaMemset(p->coop[slot], 0, sizeof(TopkCoop)));
+        CCE(cudaMalloc((void**)&p->coop[slot], sizeof(TopkOne)));
+        CCE(cudaMemsetAsync(p->coop[slot], 0, sizeof(TopkOne), s));
         p->coop_arrivals[slot] = 0;
+        p->coop_calls[slot] = 0;
     }
     const float* score = p->score[p->sidx];
     uint32_t n = (uint32_t)p->n;
-    TopkCoop* st = p->coop[slot];
-    uint32_t *bg = p->blk_gt[slot], *be = p->blk_eq[slot], *out = p->idx[slot];
+    TopkOne* st = p->coop[slot];
+    uint32_t* out = p->idx[slot];
     unsigned long long base = p->coop_arrivals[slot];
-    void* args[] = { (void*)&score, (void*)&n, (void*)&k, (void*)&worst, (void*)&st, (void*)&bg, (void*)&be, (void*)&out, (void*)&base };
-    CCE(cudaLaunchCooperativeKernel((const void*)topk_select_coop<E>, dim3((unsigned)grid), dim3(256), args, 0, s));
+    uint32_t parity = p->coop_calls[slot] & 1u;
+    void* args[] = { (void*)&score, (void*)&n, (void*)&k, (void*)&worst, (void*)&st, (void*)&out, (void*)&base, (void*)&parity };
+    CCE(cudaLaunchCooperativeKernel((const void*)topk_select_coop<E>, dim3((unsigned)grid), dim3(TOPK1_THREADS), args, 0, s));
     c->launches += 1;
-    p->coop_arrivals[slot] += 4ull * grid;  // four grid barriers per call
+    p->coop_arrivals[slot] += 3ull * grid;  // one grid barrier per radix pass
+    p->coop_calls[slot] += 1;
     return true;
 }
 
 static bool select_top_coop(pgadev_ctx* c, pgadev_pop* p, uint32_t k, int worst, int slot, cudaStream_t s)
 {
     if (c->no_coop) return false;
-    if (select_top_coop_e<8>(c, p, k, worst, slot, s)) return true;
-    if (select_top_coop_e<16>(c, p, k, worst, slot, s)) return true;
+    const uint64_t threads = (uint64_t)c->sm_count * TOPK1_THREADS;
+    if (p->n <= threads * 8u) return select_top_coop_e<8>(c, p, k, worst, slot, s);
+    if (p->n <= threads * 16u) return select_top_coop_e<16>(c, p, k, worst, slot, s);
     return select_top_coop_e<32>(c, p, k, worst, slot, s);
 }
 
@@ -788,14 +777,8 @@ extern "C" void pgadev_select_top(pgadev_ctx* c, pgadev_pop* p, uint64_t k, int 
     uint32_t *bg = p->blk_gt[slot], *be = p->blk_eq[slot];
     const float* score = p->score[p->sidx];
     const uint32_t n = (uint32_t)p->n;
-    // A ranking routed to the side stream runs BESIDE the next generation, on the few SMs that
-    // kernel left free (pgadev_step.reserve_sms).  The cooperative kernel needs all of its
-    // blocks resident at once and would wait for the generation to drain; the five-launch
-    // form has no inter-block waits, so a small grid-stride grid makes progress in whatever
-    // room there is and has a whole generation of slack.
-    const bool beside_generation = c->route_side != 0;
-    if (!beside_generation && select_top_coop(c, p, (uint32_t)k, worst, slot, s)) return;
-    launch_select_5(c, score, n, (uint32_t)k, worst, st, bg, be, p->idx[slot], p->nb, beside_generation ? c->side_blocks : 0u, s);
+    if (select_top_coop(c, p, (uint32_t)k, worst, slot, s)) return;
+    launch_select_5(c, score, n, (uint32_t)k, worst, st, bg, be, p->idx[slot], p->nb, 0u, s);
 }
 
 extern "C" void pgadev_download_top(pgadev_ctx* c, pgadev_pop* p, int slot, uint64_t k, uint32_t* host_idx)
@@ -858,6 +841,7 @@ extern "C" void pgadev_unpack_immigrants(pgadev_ctx* c, pgadev_pop* p, uint64_t 
     const uint32_t grid = grid_for(k * (p->stride >> 2), 256, (uint32_t)c->sm_count * 8u);
     unpack_rows<<<grid, 256, 0, c->stream>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[1], (uint32_t)k, p->stride, p->inbox);
     LAUNCH_CHECK(c);
+
 }
 
 extern "C" void pgadev_side_after_main(pgadev_ctx* c)

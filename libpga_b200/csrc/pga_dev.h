@@ -52,6 +52,10 @@ void pgadev_timer_start(pgadev_ctx *);
 void pgadev_timer_stop(pgadev_ctx *);
 float pgadev_timer_ms(pgadev_ctx *); /* syncs on the stop event */
 
+/* $PGA_TRACE=1: named marks on the main stream; the report prints the mean gap per pair of marks */
+void pgadev_trace_mark(pgadev_ctx *, const char *label);
+void pgadev_trace_report(pgadev_ctx *);
+
 pgadev_pop *pgadev_pop_create(pgadev_ctx *, uint64_t size, uint32_t genome_len, int encoding);
 void pgadev_pop_destroy(pgadev_ctx *, pgadev_pop *);
 uint32_t pgadev_pop_row_words(pgadev_pop *);

@@ -632,10 +632,12 @@ static void exchange_start(pga_t *p, struct exchange *ex, float pct)
 		pgadev_reserve_boxes(p->dev, p->populations[s]->dev, cap);
 	}
 
-	/* emigrants are ranked and packed on the side stream: they only read the
-	 * generation that just finished, so this overlaps the next generation */
-	pgadev_side_after_main(p->dev);
-	pgadev_route_to_side(p->dev, 1);
+	/* Emigrants are ranked on the main stream, right behind the generation that produced
+	 * them: the single cooperative launch takes ~15 us with the whole GPU to itself, while
+	 * beside the next generation it would either wait for that kernel to drain (all of its
+	 * blocks must be resident at once) or crawl on the few SMs held back for side work.
+	 * Packing and the transfer only read the finished generation and go to the side
+	 * stream, where they overlap the next generation. */
 	uint64_t k_out[MAX_POPULATIONS];
 	memset(k_out, 0, sizeof(k_out));
 	for (int t = 0; t < count; ++t) {
@@ -649,11 +651,15 @@ static void exchange_start(pga_t *p, struct exchange *ex, float pct)
 			if (pgadev_pop_row_words(dst->dev) != pgadev_pop_row_words(src->dev)) k = 0;
 		}
 		k_out[plan[t].src_local] = k;
-		if (k) {
+		if (k)
 			pgadev_select_top(p->dev, src->dev, k, 0, 0);
-			pgadev_pack_emigrants(p->dev, src->dev, k);
-		}
 	}
+	pgadev_trace_mark(p->dev, "emigrants ranked");
+	pgadev_side_after_main(p->dev);
+	pgadev_route_to_side(p->dev, 1);
+	for (unsigned s = 0; s < K; ++s)
+		if (k_out[s])
+			pgadev_pack_emigrants(p->dev, p->populations[s]->dev, k_out[s]);
 	pgadev_route_to_side(p->dev, 0);
 	pgadev_mark_packed(p->dev);
 
@@ -695,15 +701,18 @@ static void exchange_start(pga_t *p, struct exchange *ex, float pct)
 static void exchange_finish(pga_t *p, struct exchange *ex)
 {
 	pgadev_main_after_side(p->dev);
+	pgadev_trace_mark(p->dev, "transfer waited for");
 	for (unsigned s = 0; s < p->p_count; ++s) {
 		uint64_t k = ex->k_in[s];
 		if (!k)
 			continue;
 		population_t *dst = p->populations[s];
 		pgadev_select_top(p->dev, dst->dev, k, 1, 1);
+		pgadev_trace_mark(p->dev, "victims ranked");
 		pgadev_unpack_immigrants(p->dev, dst->dev, k);
 		dst->best_in_kernel = 0;
 	}
+	pgadev_trace_mark(p->dev, "immigrants unpacked");
 	ex->active = 0;
 }
 
@@ -766,9 +775,11 @@ void pga_run_islands(pga_t *p, unsigned n, unsigned m, float pct) /* stub: src/p
 		/* while an exchange is being ranked, packed and sent on the side stream the
 		 * generation kernel leaves a few SMs free for it */
 		p->reserve_sms = ex.active ? p->reserve_conf : 0;
+		pgadev_trace_mark(p->dev, ex.active ? "generation (beside)" : "generation");
 		for (unsigned s = 0; s < p->p_count; ++s)
 			generation_async(p, p->populations[s]);
 		p->reserve_sms = 0;
+		pgadev_trace_mark(p->dev, "generation done");
 		if (pending && target_reached(p)) { /* include/pga.h:147; see pga_run */
 			for (unsigned s = 0; s < p->p_count; ++s)
 				undo_generation(p->populations[s]);
@@ -795,6 +806,7 @@ void pga_run_islands(pga_t *p, unsigned n, unsigned m, float pct) /* stub: src/p
 	pgadev_timer_stop(p->dev);
 	p->last_run_ms = pgadev_timer_ms(p->dev);
 	pgadev_ctx_sync(p->dev);
+	pgadev_trace_report(p->dev);
 }
 
 /* ---- extension surface -------------------------------------------------------- */

@@ -441,12 +441,14 @@ __global__ void __launch_bounds__(256) generation_fast(const __grid_constant__ G
 // suppressed, so the loop body has no divergent region around the shuffles.
 // This is the kernel the roofline numbers are quoted on.
 //
-// One block per SM: WPB = 8 * MINB warps in ONE block rather than MINB blocks of 8 warps, so
-// that a grid of (SMs - r) blocks leaves r SMs completely empty -- room for the emigrant
-// ranking, the packing and the NCCL send/recv kernels that run beside a generation on the
-// side stream (two half-filled SMs do not hold an NCCL block; one empty SM does).
-template <int ENC, int OBJ, int LOGG, int NB, int TB, bool EXACT, int MINB>
-__global__ void __launch_bounds__(256 * MINB, 1) generation_fused_tiled(const __grid_constant__ GenArgs a)
+// ONEBLOCK: the same 8 * MINB warps per SM as ONE block instead of MINB blocks of 8 warps, so
+// that a grid of (SMs - r) blocks leaves r SMs completely empty.  Used for the generation
+// that runs beside a migration: the packing and the NCCL send/recv kernels on the side
+// stream need whole SMs (two half-filled SMs do not hold an NCCL block; one empty SM does).
+// It costs ~1 % (72.6 against 72.0 us per OneMax generation, 552 against 527 for
+// Rastrigin), so every other generation keeps the MINB-blocks form.
+template <int ENC, int OBJ, int LOGG, int NB, int TB, bool EXACT, int MINB, bool ONEBLOCK>
+__global__ void __launch_bounds__(ONEBLOCK ? 256 * MINB : 256, ONEBLOCK ? 1 : MINB) generation_fused_tiled(const __grid_constant__ GenArgs a)
 {
     constexpr uint32_t G = 1u << LOGG, CPT = 32u / G;
     __shared__ unsigned long long warp_best[8 * MINB];
@@ -917,16 +919,27 @@ __global__ void topk2_reset(TopkState2* st)
 
 // ---- top-k select in ONE cooperative launch ------------------------------------------
 //
-// A migration is latency-bound: the 5-launch select above spends ~7 us per launch on
+// A migration is latency-bound: the five-launch select above spends ~7 us per launch on
 // launch gaps, a fresh round trip to the scores and the last-block hand-over.  Here the
-// whole selection is one kernel whose blocks are all resident (cooperative launch):
-// every thread loads its E scores ONCE and keeps the keys in registers through the
-// three radix passes, the count and the compaction; the phases are separated by four
-// grid barriers.  Every block derives the chosen digit itself from the global
-// histogram, so no block has to publish a decision.
-struct TopkCoop {
-    uint32_t hist[3][TOPK2_BINS];  // one histogram per pass; zeroed again before the kernel ends
-    unsigned long long arrive;     // monotonic barrier counter (never reset)
+// whole selection is one kernel with one block of 1024 threads per SM, all resident
+// (cooperative launch).  Every thread loads its E scores ONCE and keeps the keys in
+// registers through the three radix passes and the compaction.  Every block derives the
+// chosen digit itself from the global histogram, so no block has to publish a decision.
+//
+// Three grid barriers, one per radix pass.  There is no separate count pass: in the last pass every block
+// also publishes, for each of its 1024 digits d, how many of its candidate keys have a
+// digit >= d, and how many of its keys lie beyond the 22-bit prefix; once the digit is
+// known each block reads two numbers per lower-numbered block and has its output offset.
+// The state alternates between two copies of the histograms (parity of the call number):
+// a call clears the copy the NEXT call will use, so no barrier is spent on cleaning up.
+// ncu on the 512-block, four-barrier form this replaces: 34 us at 2^20 scores, 13 of 31
+// stall cycles per instruction at the barriers.
+#define TOPK1_THREADS 1024u
+struct TopkOne {
+    uint32_t hist[2][3][TOPK2_BINS];       // [call parity][pass][bin]
+    unsigned long long arrive;             // monotonic barrier counter (never reset)
+    uint32_t beyond[160];                  // per block: keys beyond the 22-bit prefix
+    uint32_t suffix[160][1025];            // per block: candidate keys with last digit >= d
 };
 
 __device__ __forceinline__ void grid_barrier(unsigned long long* ctr, unsigned long long target)
@@ -941,53 +954,123 @@ __device__ __forceinline__ void grid_barrier(unsigned long long* ctr, unsigned l
     __syncthreads();
 }
 
+// block-wide (1024 threads): highest bin d of h[0..nbins) with (count above d) + h[d] >= rem
+__device__ __forceinline__ void pick_digit_1024(const uint32_t* h, uint32_t nbins, uint32_t rem, uint32_t* out_digit, uint32_t* out_above,
+                                                uint32_t* scratch /* >= 32 words */)
+{
+    const uint32_t t = threadIdx.x, per = nbins / TOPK1_THREADS;  // descending: thread 0 owns the top bins
+    uint32_t mine = 0;
+    for (uint32_t j = 0; j < per; ++j) mine += h[nbins - 1u - (t * per + j)];
+    uint32_t inc = mine;
+    const uint32_t lane = t & 31u, warp = t >> 5;
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, off);
+        if ((int)lane >= off) inc += o;
+    }
+    if (lane == 31u) scratch[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {  // exclusive scan of the 32 warp totals
+        const uint32_t w = scratch[lane];
+        uint32_t wi = w;
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, wi, off);
+            if ((int)lane >= off) wi += o;
+        }
+        scratch[lane] = wi - w;
+    }
+    __syncthreads();
+    inc += scratch[warp];
+    const uint32_t excl = inc - mine;  // keys in bins owned by lower-numbered threads (= higher bins)
+    if (excl < rem && inc >= rem) {    // the crossing happens inside this thread's bins; exactly one thread
+        uint32_t above = excl;
+        for (uint32_t j = 0; j < per; ++j) {
+            const uint32_t d = nbins - 1u - (t * per + j);
+            if (above + h[d] >= rem) { *out_digit = d; *out_above = above; break; }
+            above += h[d];
+        }
+    }
+    __syncthreads();
+}
+
 template <int E>
-__global__ void __launch_bounds__(256, E == 8 ? 4 : (E == 16 ? 3 : 2)) topk_select_coop(const float* __restrict__ score, uint32_t n, uint32_t k, int worst,
-                                                        TopkCoop* st, uint32_t* blk_gt, uint32_t* blk_eq, uint32_t* out_idx,
-                                                        unsigned long long barrier_base)
+__global__ void __launch_bounds__(TOPK1_THREADS, 1) topk_select_coop(const float* __restrict__ score, uint32_t n, uint32_t k, int worst, TopkOne* st,
+                                                                     uint32_t* out_idx, unsigned long long barrier_base, uint32_t parity)
 {
     __shared__ uint32_t h[TOPK2_BINS];
-    __shared__ uint32_t scratch[16];
+    __shared__ uint32_t scratch[32];
     __shared__ uint32_t s_digit, s_above;
-    __shared__ uint32_t w_gt[8], w_eq[8];
-    __shared__ uint32_t s_before[2];
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    __shared__ uint32_t w_gt[32], w_eq[32];
+    __shared__ uint32_t s_before[2], s_beyond;
+    const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
     // warp-major layout: each warp owns 32*E consecutive scores, so index order is
     // (block, warp, round, lane) and the compaction needs no block-wide scan per round
-    const uint64_t base = ((uint64_t)blockIdx.x * 8u + warp) * (32u * E);
+    const uint64_t base = ((uint64_t)blockIdx.x * 32u + warp) * (32u * E);
     uint32_t key[E];
 #pragma unroll
     for (int r = 0; r < E; ++r) {
         const uint64_t i = base + (uint32_t)r * 32u + lane;
         key[r] = i < n ? select_key(__ldg(score + i), worst) : 0u;
     }
-    const uint64_t last_valid = n;  // elements at or past n never vote
+    // the copy of the histograms the next call will use is cleared now (it was last read two calls ago)
+    if (blockIdx.x == 0)
+        for (uint32_t i = t; i < 3u * TOPK2_BINS; i += TOPK1_THREADS) (&st->hist[parity ^ 1u][0][0])[i] = 0u;
+    unsigned long long bar = barrier_base;
 
     uint32_t prefix = 0u, mask = 0u, rem = k, total_eq = 0u;
 #pragma unroll
     for (int pass = 0; pass < 3; ++pass) {
         const uint32_t shift = pass == 0 ? 21u : (pass == 1 ? 10u : 0u);
         const uint32_t nbins = pass == 2 ? 1024u : 2048u;
-        for (uint32_t i = threadIdx.x; i < nbins; i += 256u) h[i] = 0u;
-        __syncthreads();
+        {
+            for (uint32_t i = t; i < nbins; i += TOPK1_THREADS) h[i] = 0u;
+            if (t == 0) s_beyond = 0u;
+            __syncthreads();
+            uint32_t beyond = 0u;
 #pragma unroll
-        for (int r = 0; r < E; ++r) {
-            const uint64_t i = base + (uint32_t)r * 32u + lane;
-            const bool hit = i < last_valid && (key[r] & mask) == prefix;
-            const uint32_t digit = (key[r] >> shift) & (nbins - 1u);
-            const uint32_t voters = __ballot_sync(0xFFFFFFFFu, hit);
-            if (hit) {
-                const uint32_t peers = __match_any_sync(voters, digit);
-                if ((peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&h[digit], (uint32_t)__popc(peers));
+            for (int r = 0; r < E; ++r) {
+                const uint64_t i = base + (uint32_t)r * 32u + lane;
+                const bool in = i < n;
+                const bool hit = in && (key[r] & mask) == prefix;
+                if (pass == 2) beyond += in && (key[r] & mask) > prefix;
+                const uint32_t digit = (key[r] >> shift) & (nbins - 1u);
+                const uint32_t voters = __ballot_sync(0xFFFFFFFFu, hit);
+                if (hit) {  // one shared-memory atomic per distinct digit in the warp
+                    const uint32_t peers = __match_any_sync(voters, digit);
+                    if ((peers & ((1u << lane) - 1u)) == 0u) atomicAdd(&h[digit], (uint32_t)__popc(peers));
+                }
             }
+            if (pass == 2) {
+                for (int off = 16; off >= 1; off >>= 1) beyond += __shfl_xor_sync(0xFFFFFFFFu, beyond, off);
+                if (lane == 0 && beyond) atomicAdd(&s_beyond, beyond);
+            }
+            __syncthreads();
+            for (uint32_t i = t; i < nbins; i += TOPK1_THREADS)
+                if (h[i]) atomicAdd(&st->hist[parity][pass][i], h[i]);
+            if (pass == 2) {
+                // suffix counts of this block's candidates: thread t owns digit t (1024 digits, 1024 threads)
+                const uint32_t mine = h[t];
+                uint32_t inc = mine;  // inclusive scan from the top digit down = reverse-ordered scan
+                // scan in reversed thread order: use lane' = 31 - lane, warp' = 31 - warp
+                for (int off = 1; off < 32; off <<= 1) {
+                    const uint32_t o = __shfl_down_sync(0xFFFFFFFFu, inc, off);
+                    if ((int)lane + off < 32) inc += o;
+                }
+                if (lane == 0) scratch[warp] = inc;  // total of the warp's 32 digits
+                __syncthreads();
+                uint32_t above_warps = 0u;
+                for (uint32_t w2 = warp + 1u; w2 < 32u; ++w2) above_warps += scratch[w2];
+                st->suffix[blockIdx.x][t] = inc + above_warps;  // candidates with digit >= t
+                if (t == 0) {
+                    st->suffix[blockIdx.x][1024] = 0u;
+                    st->beyond[blockIdx.x] = s_beyond;
+                }
+            }
+            bar += gridDim.x;
+            grid_barrier(&st->arrive, bar);
+            for (uint32_t i = t; i < nbins; i += TOPK1_THREADS) h[i] = __ldcg(&st->hist[parity][pass][i]);
+            __syncthreads();
         }
-        __syncthreads();
-        for (uint32_t i = threadIdx.x; i < nbins; i += 256u)
-            if (h[i]) atomicAdd(&st->hist[pass][i], h[i]);
-        grid_barrier(&st->arrive, barrier_base + (unsigned long long)(pass + 1) * gridDim.x);
-        for (uint32_t i = threadIdx.x; i < nbins; i += 256u) h[i] = __ldcg(&st->hist[pass][i]);
-        __syncthreads();
-        pick_digit(h, nbins, rem, &s_digit, &s_above, scratch);
+        pick_digit_1024(h, nbins, rem, &s_digit, &s_above, scratch);
         const uint32_t d = s_digit, above = s_above;
         if (pass == 2) total_eq = h[d];
         prefix |= d << shift;
@@ -995,40 +1078,32 @@ __global__ void __launch_bounds__(256, E == 8 ? 4 : (E == 16 ? 3 : 2)) topk_sele
         rem -= above;
         __syncthreads();
     }
-    const uint32_t T = prefix, need = rem;
+    const uint32_t T = prefix, need = rem, dT = T & 1023u;
 
-    // counts of keys beyond / equal to the threshold, per warp and per block
-    uint32_t tot_g = 0u, tot_e = 0u;
-#pragma unroll
-    for (int r = 0; r < E; ++r) {
-        const uint64_t i = base + (uint32_t)r * 32u + lane;
-        tot_g += __popc(__ballot_sync(0xFFFFFFFFu, i < last_valid && key[r] > T));
-        tot_e += __popc(__ballot_sync(0xFFFFFFFFu, i < last_valid && key[r] == T));
-    }
-    if (lane == 0) { w_gt[warp] = tot_g; w_eq[warp] = tot_e; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t g2 = 0u, e2 = 0u;
-        for (uint32_t w2 = 0; w2 < 8u; ++w2) { g2 += w_gt[w2]; e2 += w_eq[w2]; }
-        blk_gt[blockIdx.x] = g2;
-        blk_eq[blockIdx.x] = e2;
-    }
-    grid_barrier(&st->arrive, barrier_base + 4ull * gridDim.x);
-
-    // the histograms are no longer read by anyone: clean them for the next call
-    if (blockIdx.x == 0)
-        for (uint32_t i = threadIdx.x; i < 3u * TOPK2_BINS; i += 256u) (&st->hist[0][0])[i] = 0u;
-
-    // selected elements in the blocks before this one
+    // selected / equal elements in the blocks before this one, from what they published in the last pass
     uint32_t bg = 0u, be = 0u;
-    for (uint32_t b2 = threadIdx.x; b2 < blockIdx.x; b2 += 256u) { bg += __ldcg(blk_gt + b2); be += __ldcg(blk_eq + b2); }
+    if (t < blockIdx.x) {
+        const uint32_t ge = __ldcg(&st->suffix[t][dT]), gt = __ldcg(&st->suffix[t][dT + 1u]);
+        bg = __ldcg(&st->beyond[t]) + gt;
+        be = ge - gt;
+    }
     for (int off = 16; off >= 1; off >>= 1) {
         bg += __shfl_xor_sync(0xFFFFFFFFu, bg, off);
         be += __shfl_xor_sync(0xFFFFFFFFu, be, off);
     }
-    if (threadIdx.x == 0) { s_before[0] = 0u; s_before[1] = 0u; }
+    if (t == 0) { s_before[0] = 0u; s_before[1] = 0u; }
     __syncthreads();
-    if (lane == 0) { atomicAdd(&s_before[0], bg); atomicAdd(&s_before[1], be); }
+    if (lane == 0 && (bg | be)) { atomicAdd(&s_before[0], bg); atomicAdd(&s_before[1], be); }
+
+    // counts of keys beyond / equal to the threshold, per warp
+    uint32_t tot_g = 0u, tot_e = 0u;
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const uint64_t i = base + (uint32_t)r * 32u + lane;
+        tot_g += __popc(__ballot_sync(0xFFFFFFFFu, i < n && key[r] > T));
+        tot_e += __popc(__ballot_sync(0xFFFFFFFFu, i < n && key[r] == T));
+    }
+    if (lane == 0) { w_gt[warp] = tot_g; w_eq[warp] = tot_e; }
     __syncthreads();
     uint32_t run_g = s_before[0], run_e = s_before[1];
     for (uint32_t w2 = 0; w2 < warp; ++w2) { run_g += w_gt[w2]; run_e += w_eq[w2]; }
@@ -1039,7 +1114,7 @@ __global__ void __launch_bounds__(256, E == 8 ? 4 : (E == 16 ? 3 : 2)) topk_sele
 #pragma unroll
     for (int r = 0; r < E; ++r) {
         const uint64_t i = base + (uint32_t)r * 32u + lane;
-        const bool gt = i < last_valid && key[r] > T, eq = i < last_valid && key[r] == T;
+        const bool gt = i < n && key[r] > T, eq = i < n && key[r] == T;
         const uint32_t mg = __ballot_sync(0xFFFFFFFFu, gt), me = __ballot_sync(0xFFFFFFFFu, eq);
         const uint32_t gt_before = run_g + __popc(mg & lt_mask), eq_before = run_e + __popc(me & lt_mask);
         const uint32_t eq_sel_before = eq_before <= eq_lo ? 0u : (eq_before >= eq_hi ? eq_hi - eq_lo : eq_before - eq_lo);

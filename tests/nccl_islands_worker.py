@@ -27,7 +27,10 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     failures = 0
-    for k_local, topology, delay in ((1, pg.TOPO_RING, 1), (2, pg.TOPO_RING, 0), (2, pg.TOPO_RANDOM, 1)):
+    # the last case arms the early stop (include/pga.h:147): every rank must leave the loop after
+    # the same generation, which takes an all-reduce of the best score over the ranks
+    for k_local, topology, delay, target in ((1, pg.TOPO_RING, 1, None), (2, pg.TOPO_RING, 0, None), (2, pg.TOPO_RANDOM, 1, None),
+                                             (1, pg.TOPO_RING, 1, 590.0)):
         g = pg.PGA(seed=SEED)
         islands.rendezvous(g, dist)
         g.set_topology(topology)
@@ -35,7 +38,11 @@ def main():
         pops = [g.create_population(SIZE, BITS, encoding=pg.GENES_BITS) for _ in range(k_local)]
         g.set_builtin_objective(pg.OBJ_ONEMAX)
         assert [p.island for p in pops] == [islands.island_id(s, rank, world) for s in range(k_local)]
-        g.run_islands(GENS, EVERY, PCT)
+        gens = GENS if target is None else 200
+        if target is not None:
+            g.set_target(target, 3)
+        g.run_islands(gens, EVERY, PCT)
+        ran = g.generations_run
         mine = {p.island: (po.digest(p.genes()), po.digest(p.scores())) for p in pops}
         gathered = [None] * world
         dist.all_gather_object(gathered, mine)
@@ -49,7 +56,13 @@ def main():
             ops = [o.create_population(SIZE, BITS, po.GENES_BITS) for _ in range(k_local * world)]
             o.set_topology(topology)
             o.set_migration_delay(delay)
-            o.run_islands(GENS, EVERY, PCT)
+            if target is not None:
+                o.set_target(target, 3)
+            o.run_islands(gens, EVERY, PCT)
+            if target is not None:
+                ok = ran == o.generations_run and 0 < ran < gens
+                failures += 0 if ok else 1
+                print(f"early stop: ran {ran} generations, oracle {o.generations_run}: {'ok' if ok else 'MISMATCH'}", flush=True)
             for i, p in enumerate(ops):
                 ok = got[i] == (po.digest(p.genes()), po.digest(p.scores()))
                 failures += 0 if ok else 1
