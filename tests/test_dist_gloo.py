@@ -5,7 +5,7 @@ global island numbering (island = local * world + rank), the exchange plan compu
 by the C library (pgax_plan_exchange, a pure host function) and the order in which
 sends and receives are posted.  The populations themselves are held by the CPU oracle
 (this is a test: the product never computes on the CPU).  Each rank runs its islands
-through libpga_b200.islands.run_islands_host with torch.distributed point-to-point
+through tests/islands_host_schedule.run_islands_host with torch.distributed point-to-point
 calls; the result must equal ONE oracle process running all islands.
 """
 import os
@@ -26,7 +26,7 @@ SIZE, LENGTH, GENS, EVERY, PCT = 600, 256, 9, 2, 4.0
 
 
 class OracleEngine:
-    """Adapter: the engine interface of islands.run_islands_host over oracle populations."""
+    """Adapter: the engine interface of run_islands_host over oracle populations."""
 
     def __init__(self, po, oracle, pops):
         self.po, self.o, self.islands = po, oracle, pops
@@ -61,6 +61,8 @@ def worker(rank, port, k_local, topology, delay, out):
     dist.init_process_group("gloo", rank=rank, world_size=WORLD)
     from oracle import pyoracle as po
     from libpga_b200 import islands
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import islands_host_schedule
     o = po.Oracle(99)
     o.set_builtin_objective(po.OBJ_ONEMAX)
     pops = [o.create_population(SIZE, LENGTH, po.GENES_BITS, island=islands.island_id(s, rank, WORLD)) for s in range(k_local)]
@@ -78,7 +80,7 @@ def worker(rank, port, k_local, topology, delay, out):
         dist.recv(t, src)
         return t.numpy().view(np.uint32)
 
-    islands.run_islands_host(eng, GENS, EVERY, PCT, seed=99, topology=topology, delay=delay, rank=rank, world=WORLD,
+    islands_host_schedule.run_islands_host(eng, GENS, EVERY, PCT, seed=99, topology=topology, delay=delay, rank=rank, world=WORLD,
                              send=send, recv=recv)
     for s, p in enumerate(pops):
         out[islands.island_id(s, rank, WORLD)] = (po.digest(p.genes()), po.digest(p.scores()))
