@@ -48,17 +48,19 @@ WORKLOADS = {
 
 
 KERNELS = {
-    "onemax": "generation_fused_tiled<ENC_BITS, OBJ_ONEMAX, LOGG=3, NB=1, TB=8>",
-    "rastrigin": "generation_fused_tiled<ENC_F32, OBJ_RASTRIGIN, LOGG=5, NB=2, TB=2>",
+    "onemax": "generation_fused_tiled<ENC_BITS, OBJ_ONEMAX, LOGG=3, NB=1, TB=8, EXACT, MINB=2, ONEBLOCK=0>",
+    "rastrigin": "generation_fused_tiled<ENC_F32, OBJ_RASTRIGIN, LOGG=5, NB=2, TB=2, EXACT, MINB=3, ONEBLOCK=0>",
     "test1": "generation_hooks<PH_FUSED> (user objective through a device function pointer)",
     "tsp": "generation_hooks<CROSSOVER+MUTATE> then generation_hooks<EVALUATE> (user hooks through device function pointers; split chosen by timing)",
 }
 
 
-FABRIC_NOTE = {
-    "onemax": "bound by SM<->L2 sector throughput, not HBM: 516 B per child cross L2 (4 score-gather sectors + 2 parents + child) "
-              "= 539 MB per launch at ~7.8 TB/s (ncu, profiles/r1_sweeps.md); that caps frac near 0.59",
-    "rastrigin": "HBM-bound: 3 population passes of DRAM traffic (2 gathered parents + 1 child) = 3.19 GB per launch at 93 % of the measured peak",
+BOUND_NOTE = {
+    "onemax": "516 B cross L2 per child (4 score-gather sectors + 2 parents + child) for 256 B algorithmic; at this size the kernel "
+              "runs at the measured ceiling of its own access pattern for those bytes (profiles/r2_sweeps.md sections 1-2); "
+              "no unit is above 67 % of its peak (ncu, profiles/r2_ncu_onemax_tiled.txt)",
+    "rastrigin": "3 population passes of DRAM traffic (2 gathered parents + 1 child) = 3.19 GB per launch at 93 % of the measured "
+                 "peak, and 335 M warp instructions at 59 % issue efficiency: co-bound (profiles/r2_sweeps.md section 3)",
 }
 
 
@@ -469,7 +471,7 @@ def main():
                      "traffic": ncu_traffic(args.workload), "kernel": KERNELS[args.workload],
                      "algorithmic_bytes_per_launch": 2 * w["size"] * gb, "avg_launch_ms": kernel_ms / n_launch,
                      "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
-                     "note": FABRIC_NOTE.get(args.workload)},
+                     "note": BOUND_NOTE.get(args.workload)},
     }
     g.deinit()
     if args.workload == "onemax" and not args.no_c5 and not args.size:
