@@ -39,6 +39,17 @@ libpga.a: $(OBJS)
 libpga_b200/libpga_b200.so: $(OBJS) $(DEMO)
 	$(NVCC) $(ARCH) -shared -Xcompiler -fPIC $(OBJS) $(DEMO) -o $@ -lcudart -ldl
 
+# the same library with every row / score / slot index asserted on the device (-DPGA_DEBUG);
+# tests/test_gpu_debug_build.py runs parity cases through it (the pool has no compute-sanitizer)
+debug: libpga_b200/libpga_b200_dbg.so
+
+$(BUILD)/pga_dev_dbg.o: $(SRC)/pga_dev.cu $(KHDRS)
+	@mkdir -p $(BUILD)
+	$(NVCC) $(NVFLAGS) -DPGA_DEBUG -dc $< -o $@
+
+libpga_b200/libpga_b200_dbg.so: $(BUILD)/pga_host.o $(BUILD)/pga_dev_dbg.o $(DEMO)
+	$(NVCC) $(ARCH) -shared -Xcompiler -fPIC $(BUILD)/pga_host.o $(BUILD)/pga_dev_dbg.o $(DEMO) -o $@ -lcudart -ldl
+
 oracle:
 	$(MAKE) -C oracle
 
@@ -46,6 +57,6 @@ ref:
 	bash oracle/build_ref.sh
 
 clean:
-	rm -rf $(BUILD) libpga.a libpga_b200/libpga_b200.so
+	rm -rf $(BUILD) libpga.a libpga_b200/libpga_b200.so libpga_b200/libpga_b200_dbg.so
 
-.PHONY: all oracle ref clean
+.PHONY: all debug oracle ref clean

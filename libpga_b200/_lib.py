@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libpga_b200.so")
+# $PGA_B200_SO selects another build of the same library (the asserting debug build, `make debug`)
+SO_PATH = os.environ.get("PGA_B200_SO") or os.path.join(_HERE, "libpga_b200.so")
 
 _vp, _u64, _u32, _i32, _f32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_float
 _ul, _ui, _sz = C.c_ulong, C.c_uint, C.c_size_t

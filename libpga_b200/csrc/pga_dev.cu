@@ -829,7 +829,7 @@ extern "C" void pgadev_pack_emigrants(pgadev_ctx* c, pgadev_pop* p, uint64_t k)
     use_device(c);
     ensure_boxes(c, p, k);
     const uint32_t grid = grid_for(k * (p->stride >> 2), 256, (uint32_t)c->sm_count * 8u);
-    pack_rows<<<grid, 256, 0, work_stream(c)>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[0], (uint32_t)k, p->stride, p->outbox);
+    pack_rows<<<grid, 256, 0, work_stream(c)>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[0], (uint32_t)k, p->stride, p->outbox, (uint32_t)p->n);
     LAUNCH_CHECK(c);
 }
 
@@ -843,7 +843,7 @@ extern "C" void pgadev_unpack_immigrants(pgadev_ctx* c, pgadev_pop* p, uint64_t 
 {
     use_device(c);
     const uint32_t grid = grid_for(k * (p->stride >> 2), 256, (uint32_t)c->sm_count * 8u);
-    unpack_rows<<<grid, 256, 0, c->stream>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[1], (uint32_t)k, p->stride, p->inbox);
+    unpack_rows<<<grid, 256, 0, c->stream>>>(p->genes[p->gidx], p->score[p->sidx], p->idx[1], (uint32_t)k, p->stride, p->inbox, (uint32_t)p->n);
     LAUNCH_CHECK(c);
 
 }

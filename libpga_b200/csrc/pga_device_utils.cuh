@@ -10,6 +10,16 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// Bounds checks for the debug build (make debug: -DPGA_DEBUG, libpga_b200_dbg.so).  The GPU
+// pool has no compute-sanitizer, so every index that addresses a population row, a score or an
+// output slot is asserted there; the release build compiles them away.
+#ifdef PGA_DEBUG
+#include <assert.h>
+#define PGA_ASSERT(x) assert(x)
+#else
+#define PGA_ASSERT(x) ((void)0)
+#endif
+
 namespace pgak {
 
 // ---- Philox4x32-10 --------------------------------------------------------

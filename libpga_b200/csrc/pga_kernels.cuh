@@ -59,6 +59,7 @@ struct GenArgs {
 __device__ __forceinline__ uint32_t tournament(const float* __restrict__ score, float ua, float ub, float nf, uint32_t n)
 {
     const uint32_t a = draw_index(ua, nf, n), b = draw_index(ub, nf, n);
+    PGA_ASSERT(a < n && b < n);
     const float sa = __ldg(score + a), sb = __ldg(score + b);
     return sa < sb ? b : a;
 }
@@ -78,6 +79,7 @@ __device__ __forceinline__ uint32_t tournament_of(const DrawCtx& d, const float*
         if ((j >> 2) != have) { have = j >> 2; w = draw_block(d, STREAM_ROW, child, have); }
         const uint32_t x = (j & 3u) == 0 ? w.x : (j & 3u) == 1 ? w.y : (j & 3u) == 2 ? w.z : w.w;
         const uint32_t c = draw_index(to_uniform(x), nf, n);
+        PGA_ASSERT(c < n);
         const float sc = __ldg(score + c);
         if (i == 0 || sbest < sc) { best = c; sbest = sc; }
     }
@@ -256,6 +258,7 @@ __global__ void __launch_bounds__(128) generation_hooks(const __grid_constant__ 
             if (a.mut != nullptr) {
                 a.mut(c, s_rnd + (size_t)t * S, a.len);  // src/pga.cu:341
             } else if (u1 <= PGA_MUTATION_CHANCE) {      // src/pga.cu:127-133
+                PGA_ASSERT(draw_index(u0, a.lenf, a.len) < a.len);
                 c[draw_index(u0, a.lenf, a.len)] = u2;
             }
         }
@@ -357,6 +360,7 @@ __global__ void __launch_bounds__(256) generation_fast(const __grid_constant__ G
                 for (uint32_t b = gl; b < nblk; b += G) {
                     uint4 c;
                     if (PH & PH_CROSSOVER) {
+                        PGA_ASSERT(q1 < a.n && q2 < a.n && b < nblk);
                         const uint4 x = __ldg(cur + (size_t)q1 * nblk + b);
                         const uint4 y = __ldg(cur + (size_t)q2 * nblk + b);
                         if (ENC == ENC_BITS) {
@@ -494,6 +498,7 @@ __global__ void __launch_bounds__(ONEBLOCK ? 256 * MINB : 256, ONEBLOCK ? 1 : MI
                 const uint32_t src_lane = (tile0 + tb) * CPT + grp;
                 const uint32_t q1 = __shfl_sync(0xFFFFFFFFu, p1, src_lane);
                 const uint32_t q2 = __shfl_sync(0xFFFFFFFFu, p2, src_lane);
+                PGA_ASSERT(q1 < a.n && q2 < a.n);
                 const uint4* r1 = cur + (size_t)q1 * nblk + gl;
                 const uint4* r2 = cur + (size_t)q2 * nblk + gl;
 #pragma unroll
@@ -558,6 +563,7 @@ __global__ void __launch_bounds__(ONEBLOCK ? 256 * MINB : 256, ONEBLOCK ? 1 : MI
                             if (EXACT || j + 2 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.z));
                             if (EXACT || j + 3 < a.len) facc = obj_accumulate<OBJ>(facc, __uint_as_float(c.w));
                         }
+                        PGA_ASSERT(!valid || (child < a.n && b < (a.stride >> 2)));
                         if (valid) store_row_block(out + nb * G, c);
                     }
                 }
@@ -1118,6 +1124,7 @@ __global__ void __launch_bounds__(TOPK1_THREADS, 1) topk_select_coop(const float
         const uint32_t mg = __ballot_sync(0xFFFFFFFFu, gt), me = __ballot_sync(0xFFFFFFFFu, eq);
         const uint32_t gt_before = run_g + __popc(mg & lt_mask), eq_before = run_e + __popc(me & lt_mask);
         const uint32_t eq_sel_before = eq_before <= eq_lo ? 0u : (eq_before >= eq_hi ? eq_hi - eq_lo : eq_before - eq_lo);
+        PGA_ASSERT(!(gt || (eq && eq_before >= eq_lo && eq_before < eq_hi)) || gt_before + eq_sel_before < k);
         if (gt) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
         else if (eq && eq_before >= eq_lo && eq_before < eq_hi) out_idx[gt_before + eq_sel_before] = (uint32_t)i;
         run_g += __popc(mg);
@@ -1128,7 +1135,7 @@ __global__ void __launch_bounds__(TOPK1_THREADS, 1) topk_select_coop(const float
 // ---- migration payloads ---------------------------------------------------------
 // box layout: k rows of `stride` words, then k scores
 __global__ void pack_rows(const uint32_t* __restrict__ rows, const float* __restrict__ score, const uint32_t* __restrict__ idx,
-                          uint32_t k, uint32_t stride, uint32_t* box)
+                          uint32_t k, uint32_t stride, uint32_t* box, uint32_t n)
 {
     const uint32_t nblk = stride >> 2;
     const uint64_t total = (uint64_t)k * nblk;
@@ -1136,13 +1143,14 @@ __global__ void pack_rows(const uint32_t* __restrict__ rows, const float* __rest
     for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (uint64_t)gridDim.x * blockDim.x) {
         const uint32_t j = (uint32_t)(e / nblk), b = (uint32_t)(e % nblk);
         const uint32_t src = idx[j];
+        PGA_ASSERT(src < n);
         reinterpret_cast<uint4*>(box)[e] = __ldg(reinterpret_cast<const uint4*>(rows) + (size_t)src * nblk + b);
         if (b == 0) box_score[j] = score[src];
     }
 }
 
 __global__ void unpack_rows(uint32_t* rows, float* score, const uint32_t* __restrict__ idx, uint32_t k, uint32_t stride,
-                            const uint32_t* __restrict__ box)
+                            const uint32_t* __restrict__ box, uint32_t n)
 {
     const uint32_t nblk = stride >> 2;
     const uint64_t total = (uint64_t)k * nblk;
@@ -1150,6 +1158,7 @@ __global__ void unpack_rows(uint32_t* rows, float* score, const uint32_t* __rest
     for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (uint64_t)gridDim.x * blockDim.x) {
         const uint32_t j = (uint32_t)(e / nblk), b = (uint32_t)(e % nblk);
         const uint32_t dst = idx[j];
+        PGA_ASSERT(dst < n);
         reinterpret_cast<uint4*>(rows)[(size_t)dst * nblk + b] = __ldg(reinterpret_cast<const uint4*>(box) + e);
         if (b == 0) score[dst] = box_score[j];
     }
@@ -1157,7 +1166,7 @@ __global__ void unpack_rows(uint32_t* rows, float* score, const uint32_t* __rest
 
 __global__ void gather_scores(const float* __restrict__ score, const uint32_t* __restrict__ idx, uint32_t k, float* out)
 {
-    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < k; j += gridDim.x * blockDim.x) out[j] = score[idx[j]];
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < k; j += gridDim.x * blockDim.x) out[j] = score[idx[j]];  // idx from the select: < n (asserted there)
 }
 
 // host rows are unpadded; device rows are padded to a multiple of 4 words
