@@ -14,7 +14,7 @@ ncu --set full --clock-control none --import-source on -k regex:generation_fused
 CMD="python bench.py --workload rastrigin --steps 1 --warmup 3 --gens 3 --no-cpu-baseline"
 $CMD > gpurun_out/r2p_plain_full2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:generation_fused_tiled -s 6 -c 2 -o gpurun_out/prof_rastrigin_r2 $CMD > gpurun_out/r2p_ncu_full_rastrigin.log 2>&1
-CMD="python scripts/dbg_select.py 1048576"
+CMD="python scripts/time_select.py 1048576"
 $CMD > gpurun_out/r2p_plain_sel.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:topk_select_coop -s 4 -c 2 -o gpurun_out/prof_select_r2 $CMD > gpurun_out/r2p_ncu_full_select.log 2>&1
 # gpurun brings back at most 64 MiB: summarise here, keep only the OneMax report
