@@ -343,6 +343,7 @@ def main():
     ap.add_argument("--workload", default="onemax", choices=sorted(WORKLOADS))
     ap.add_argument("--gens", type=int, default=100, help="generations per step")
     ap.add_argument("--size", type=int, default=0, help="override the population size")
+    ap.add_argument("--length", type=int, default=0, help="override the genome length (sweeps only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--islands", type=int, default=1, help="islands per GPU (BASELINE config 5: 8 islands over N GPUs)")
     ap.add_argument("--migrate-every", type=int, default=10)
@@ -354,6 +355,9 @@ def main():
     if args.size:
         w["size"] = args.size
         w["label"] += f" (size overridden to {args.size})"
+    if args.length:
+        w["length"] = args.length
+        w["label"] += f" (length overridden to {args.length})"
 
     if args.impl == "reference":
         run_reference_arm(args, w, emit)
@@ -474,7 +478,7 @@ def main():
                      "note": BOUND_NOTE.get(args.workload)},
     }
     g.deinit()
-    if args.workload == "onemax" and not args.no_c5 and not args.size:
+    if args.workload == "onemax" and not args.no_c5 and not args.size and not args.length:
         c5 = run_c5(args, pg, islands, dist, torch, stream, world, distributed)
         line["c5"] = c5
     if distributed:

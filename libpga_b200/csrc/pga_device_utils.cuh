@@ -79,10 +79,27 @@ __device__ __forceinline__ bool draw_above_half(uint32_t x)
 // L2 eviction-priority hints (createpolicy evict_last on the gathers, evict_first
 // on the child stores, and the other combinations) were measured on B200 and made
 // no difference to time or DRAM traffic (profiles/r1_sweeps.md), so none are used.
+// Parent rows bypass L1 (each is read once per SM).  In L2 a bare L1::no_allocate load is
+// treated as evict-first too -- it times exactly like an explicit L2::evict_first policy --
+// which throws away what L2 can reuse: a winner is the parent of several children, and the
+// generation being written turns into the one being read.  With KEEP the load names the
+// normal L2 policy instead.  Measured per generation (profiles/r2_l2_hint_forms.log,
+// r2_ab_row_loads.log): 128-byte rows 72.0 -> 66.0 us at 2^20, 144.8 -> 133.4 at 2^21,
+// 677.8 -> 662.6 at 2^23; 512-byte rows 266.1 -> 251.4; 768-byte rows 538.4 -> 533.1;
+// rows of 1 KiB go the other way (525.3 -> 538.1) and keep the bare form.
+template <bool KEEP>
 __device__ __forceinline__ uint4 load_row_block(const uint4* p)
 {
     uint4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    if (KEEP) {
+        uint64_t pol;
+        asm("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                     : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                     : "l"(p), "l"(pol));
+    } else {
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    }
     return v;
 }
 

@@ -222,8 +222,8 @@ __global__ void __launch_bounds__(128) generation_hooks(const __grid_constant__ 
                     uint4 x[4], y[4];
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        x[u] = load_row_block(cur4 + (size_t)q1[u] * nblk + b);
-                        y[u] = load_row_block(cur4 + (size_t)q2[u] * nblk + b);
+                        x[u] = load_row_block<false>(cur4 + (size_t)q1[u] * nblk + b);
+                        y[u] = load_row_block<false>(cur4 + (size_t)q2[u] * nblk + b);
                     }
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
@@ -455,6 +455,7 @@ template <int ENC, int OBJ, int LOGG, int NB, int TB, bool EXACT, int MINB, bool
 __global__ void __launch_bounds__(ONEBLOCK ? 256 * MINB : 256, ONEBLOCK ? 1 : MINB) generation_fused_tiled(const __grid_constant__ GenArgs a)
 {
     constexpr uint32_t G = 1u << LOGG, CPT = 32u / G;
+    constexpr bool KEEP_L2 = (uint32_t)NB * G * 16u < 1024u;  // rows under 1 KiB: see load_row_block
     __shared__ unsigned long long warp_best[8 * MINB];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -504,8 +505,8 @@ __global__ void __launch_bounds__(ONEBLOCK ? 256 * MINB : 256, ONEBLOCK ? 1 : MI
 #pragma unroll
                 for (int nb = 0; nb < NB; ++nb) {
                     if (EXACT || gl + (uint32_t)nb * G < nblk) {
-                        x[tb][nb] = load_row_block(r1 + nb * G);
-                        y[tb][nb] = load_row_block(r2 + nb * G);
+                        x[tb][nb] = load_row_block<KEEP_L2>(r1 + nb * G);
+                        y[tb][nb] = load_row_block<KEEP_L2>(r2 + nb * G);
                     }
                 }
             }
