@@ -56,9 +56,10 @@ KERNELS = {
 
 
 BOUND_NOTE = {
-    "onemax": "516 B cross L2 per child (4 score-gather sectors + 2 parents + child) for 256 B algorithmic; at this size the kernel "
-              "runs at the measured ceiling of its own access pattern for those bytes (profiles/r2_sweeps.md sections 1-2); "
-              "no unit is above 67 % of its peak (ncu, profiles/r2_ncu_onemax_tiled.txt)",
+    "onemax": "516 B cross L2 per child (4 score-gather sectors + 2 parents + child) for 256 B algorithmic; latency-bound at "
+              "4 warps per scheduler (3.8 of 9.5 warp-cycles per issue on the long scoreboard), no unit above 57 % of its peak; "
+              "L2 hit rate 33 % since the row loads name the normal L2 policy, DRAM 169 MB read + 104 MB written per launch "
+              "(ncu, profiles/r2_ncu_onemax.txt; profiles/r2_sweeps.md sections 1-2b)",
     "rastrigin": "3 population passes of DRAM traffic (2 gathered parents + 1 child) = 3.19 GB per launch at 93 % of the measured "
                  "peak, and 335 M warp instructions at 59 % issue efficiency: co-bound (profiles/r2_sweeps.md section 3)",
 }
