@@ -222,7 +222,37 @@ def run_reference_arm(args, w, emit):
         "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
+    if n_islands == 1:
+        rg = reference_gpu(w, args)  # test1 only: the reference's own GPU library runs this workload
+        if rg:
+            line["reference_gpu"] = rg
     emit(line)
+
+
+def reference_gpu(w, args):
+    """The reference's own GPU library (src/pga.cu rebuilt for sm_100a, oracle/build_ref.sh) and this
+    repository's libpga.a behind the SAME program (oracle/ref_time.cu + the reference demo's objective),
+    wall-clock pga_run on this box's GPU.  Only the reference's test/ workload: its kernels need
+    64 * genome_len * 4 bytes of shared memory per block and have no packed-bit genomes."""
+    import subprocess
+    if w.get("hook") != "sum_obj" or w["length"] != 100:
+        return None
+    out = {}
+    for name in ("ref1", "ours1"):
+        exe = os.path.join(ROOT, "oracle", "_ref", "time", name)
+        if not os.path.exists(exe):
+            return {"unavailable": "oracle/_ref/time not built (oracle/build_ref.sh needs the reference checkout)"}
+        r = subprocess.run([exe, "--size", str(w["size"]), "--gens", str(args.gens), "--reps", "5"],
+                           capture_output=True, text=True, timeout=600)
+        if r.returncode != 0:
+            return {"unavailable": f"{name} exited {r.returncode}: {r.stderr[-200:]}"}
+        out[name] = json.loads(r.stdout.strip().splitlines()[-1])
+    ref, ours = out["ref1"], out["ours1"]
+    return {"what": "pga_run wall clock, /root/reference/test/test.cu's workload through oracle/ref_time.cu: the unmodified reference "
+                    "library rebuilt for sm_100a (cuRAND, time seed) against this repository's libpga.a, same program, same GPU",
+            "reference": {"value": ref["evals_per_s"], "unit": "evals/s", "us_per_generation": ref["us_per_generation"]},
+            "this_library": {"value": ours["evals_per_s"], "unit": "evals/s", "us_per_generation": ours["us_per_generation"]},
+            "size": ref["size"], "genome_len": ref["genome_len"], "generations": ref["generations"]}
 
 
 def cpu_baseline(w, cores=None):
@@ -489,6 +519,9 @@ def main():
         line["islands_parity"] = {"checked": False, "why": "single GPU: no NCCL exchange to check (tests/test_gpu_islands.py covers the one-GPU islands)"}
     if rank == 0 and not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline(w)                  # all host cores (OpenMP over individuals)
+        rg = reference_gpu(w, args)                             # the reference's own GPU library, where it can run
+        if rg:
+            line["reference_gpu"] = rg
         line["cpu_baseline_serial"] = cpu_baseline(w, cores=1)  # the serial oracle, one core
     if distributed:
         dist.barrier()

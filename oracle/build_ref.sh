@@ -9,6 +9,8 @@
 #   oracle/_ref/pin/pin{1,2,3}      the reference library + its demo hooks, cuRAND replaced at
 #                                   link time by oracle/curand_shim.c, compared lock-step with
 #                                   the oracle (oracle/ref_pin.cu)
+#   oracle/_ref/time/{ref1,ours1}   oracle/ref_time.cu: pga_run timed on the test/ workload with
+#                                   the reference library and with this repository's libpga.a
 # Only the architecture flag differs from the reference's Makefiles (-arch=sm_20 is
 # rejected by nvcc 12.9; Makefile:2, test/Makefile:2-3).  Outputs are git-ignored but
 # travel to the GPU box.  Test infrastructure, not product.
@@ -56,5 +58,17 @@ for t in test test2 test3; do
         -Xcompiler -fopenmp -lgomp -lm -o "$OUT/pin/pin$i"
     i=$((i + 1))
 done
+
+# ---- timing: pga_run on the reference's test/ workload, reference library vs this one ------
+# oracle/ref_time.cu + the reference demo's objective (main renamed); the same source is
+# linked once against libpga_ref.a + cuRAND and once against this repository's libpga.a.
+mkdir -p "$OUT/time"
+nvcc -dc $ARCH -w -Dmain=reference_demo_main "$REF/test/test.cu" -I"$REF/include" -o "$OUT/obj/test_hooks_ref.o"
+nvcc -dc $ARCH -w "$HERE/ref_time.cu" -I"$REF/include" -o "$OUT/obj/time_ref.o"
+nvcc $ARCH "$OUT/obj/time_ref.o" "$OUT/obj/test_hooks_ref.o" "$OUT/libpga_ref.a" -lcurand -o "$OUT/time/ref1"
+nvcc -dc $ARCH -w -Dmain=reference_demo_main "$REF/test/test.cu" -I"$ROOT/include" -o "$OUT/obj/test_hooks_ours.o"
+nvcc -dc $ARCH -w "$HERE/ref_time.cu" -I"$ROOT/include" -o "$OUT/obj/time_ours.o"
+nvcc $ARCH "$OUT/obj/time_ours.o" "$OUT/obj/test_hooks_ours.o" -L"$ROOT" -lpga -lcurand -o "$OUT/time/ours1"
+
 rm -rf "$OUT/obj"
-ls -la "$OUT" "$OUT/ref" "$OUT/dropin" "$OUT/pin"
+ls -la "$OUT" "$OUT/ref" "$OUT/dropin" "$OUT/pin" "$OUT/time"

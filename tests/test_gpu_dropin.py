@@ -81,3 +81,20 @@ def test_reference_itself_runs_on_this_gpu():
     out = run(os.path.join(REF, "test1"), 0)
     v = float(out.strip().split("\n")[0])
     assert 50.0 < v <= 100.0
+
+
+def test_timing_harness_runs_with_both_libraries():
+    # oracle/ref_time.cu (bench.py's reference_gpu leg): one source against the reference library
+    # and against this repository's libpga.a; here only that both run and report the workload
+    import json
+    import subprocess
+    out = {}
+    for name in ("ref1", "ours1"):
+        exe = os.path.join(ROOT, "oracle", "_ref", "time", name)
+        if not os.path.exists(exe):
+            pytest.skip(f"{exe} not built (run oracle/build_ref.sh where /root/reference exists)")
+        r = subprocess.run([exe, "--size", "4000", "--gens", "5", "--reps", "2"], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        out[name] = json.loads(r.stdout.strip().splitlines()[-1])
+    for d in out.values():
+        assert (d["size"], d["genome_len"], d["generations"]) == (4000, 100, 5) and d["seconds_mean"] > 0
